@@ -1,0 +1,412 @@
+// BatchNorm (training + eval) fused with ReLU and the residual add, forward and backward, on NHWC bf16.
+// Memory-bound streaming kernels: 16-byte vectors (8 channels) per thread, fp32 statistics, two-pass
+// deterministic reductions (per-CTA partials -> finalize).  The finalize kernels optionally reduce the
+// statistics across GPUs through peer-mapped symmetric memory (SyncBatchNorm) without a separate collective.
+//
+// Replaces aten::native_batch_norm(+_backward), relu_, add_, threshold_backward reached by the reference through
+// torchvision's BasicBlock/Bottleneck (reference resnet/main.py:76,121,123) and, for the cross-GPU variant,
+// torch.nn.SyncBatchNorm's all_gather / all_reduce of statistics.
+#include "b200ddp.h"
+#include "ptx.cuh"
+#include "xgpu.cuh"
+
+namespace b2 {
+
+constexpr int kBnThreads = 256;
+constexpr int kMaxPartialBlocks = 1184;  // 148 SMs x 8
+
+struct Vec8 {
+  float v[8];
+};
+B2_DEVICE Vec8 load_bf16x8(const __nv_bfloat16* p) {
+  uint4 u = *reinterpret_cast<const uint4*>(p);
+  Vec8 r;
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y; r.v[4] = c.x; r.v[5] = c.y; r.v[6] = d.x; r.v[7] = d.y;
+  return r;
+}
+B2_DEVICE void store_bf16x8(__nv_bfloat16* p, const Vec8& r) {
+  uint4 u;
+  u.x = pack_bf16x2(r.v[0], r.v[1]); u.y = pack_bf16x2(r.v[2], r.v[3]);
+  u.z = pack_bf16x2(r.v[4], r.v[5]); u.w = pack_bf16x2(r.v[6], r.v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+B2_DEVICE Vec8 load_f32x8(const float* p) {
+  Vec8 r;
+  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
+// Reduce per-thread 8-channel accumulators over the rows handled by one CTA and write partial[blk][which][C].
+template <int NACC>
+B2_DEVICE void block_reduce_store(float (&acc)[NACC][8], float* smem, float* partial, int C, int C8, int RP, int cv,
+                                  int r, int nblk_stride /* = C */) {
+  // smem layout: [NACC][RP][C]
+  for (int a = 0; a < NACC; ++a)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) smem[(a * RP + r) * C + cv * 8 + j] = acc[a][j];
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NACC * C; idx += blockDim.x) {
+    const int a = idx / C, c = idx - a * C;
+    float s = 0.f;
+    for (int rr = 0; rr < RP; ++rr) s += smem[(a * RP + rr) * C + c];
+    partial[(size_t)blockIdx.x * NACC * C + idx] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ forward stats
+__global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* partial,
+                                                              long long M, int C, long long rows_per_blk) {
+  extern __shared__ float smem[];
+  const int C8 = C >> 3, RP = kBnThreads / C8;
+  const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+  const long long row0 = blockIdx.x * rows_per_blk;
+  const long long row1 = min(M, row0 + rows_per_blk);
+  if (r < RP) {
+    for (long long row = row0 + r; row < row1; row += RP) {
+      Vec8 v = load_bf16x8(y + row * C + cv * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        acc[0][j] += v.v[j];
+        acc[1][j] += v.v[j] * v.v[j];
+      }
+    }
+    block_reduce_store<2>(acc, smem, partial, C, C8, RP, cv, r, C);
+  } else {
+    __syncthreads();
+  }
+}
+
+// Finalize: partial sums -> mean / invstd / running stats / fused scale+shift.  With world > 1 the per-GPU
+// totals (sum, sumsq, count) are exchanged through symmetric memory inside this kernel (SyncBatchNorm).
+__global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* running_mean, float* running_var, long long* num_batches_tracked,
+                                   float momentum, float eps, float* mean_out, float* invstd_out, float* scale_out,
+                                   float* shift_out, XgpuCtx xg, int slot_off) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  float s = 0.f, ss = 0.f;
+  if (c < C) {
+    for (int b = 0; b < nblk; ++b) {
+      s += partial[(size_t)b * 2 * C + c];
+      ss += partial[(size_t)b * 2 * C + C + c];
+    }
+  }
+  float total = count;
+  if (xg.world > 1) {
+    // Publish this GPU's totals, then read everybody's in rank order (identical result on every rank).
+    float* mine = xg.data[xg.rank] + slot_off;
+    if (c < C) {
+      mine[c] = s;
+      mine[C + c] = ss;
+    }
+    if (c == 0) mine[2 * C] = count;
+    xgpu_barrier(xg, /*channel=*/blockIdx.x);
+    s = 0.f; ss = 0.f; total = 0.f;
+    for (int rk = 0; rk < xg.world; ++rk) {
+      const float* peer = xg.data[rk] + slot_off;
+      if (c < C) {
+        s += ld_relaxed_sys_f32(peer + c);
+        ss += ld_relaxed_sys_f32(peer + C + c);
+      }
+      total += ld_relaxed_sys_f32(peer + 2 * C);
+    }
+    xgpu_barrier(xg, blockIdx.x);  // nobody overwrites its slot while a peer may still be reading it
+  }
+  if (c >= C) return;
+  const float mean = s / total;
+  float var = ss / total - mean * mean;
+  var = fmaxf(var, 0.f);
+  const float invstd = rsqrtf(var + eps);
+  mean_out[c] = mean;
+  invstd_out[c] = invstd;
+  const float sc = gamma[c] * invstd;
+  scale_out[c] = sc;
+  shift_out[c] = beta[c] - mean * sc;
+  if (running_mean) {
+    const float unbiased = total > 1.f ? var * total / (total - 1.f) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    if (c == 0 && num_batches_tracked) *num_batches_tracked += 1;
+  }
+}
+
+// Eval mode: scale/shift from running statistics.
+__global__ void bn_eval_coeffs_kernel(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
+                                      float eps, float* scale, float* shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = gamma[c] * rsqrtf(rv[c] + eps);
+  scale[c] = sc;
+  shift[c] = beta[c] - rm[c] * sc;
+}
+
+// ------------------------------------------------------------------------------------------------ forward apply
+template <bool RELU, bool RES>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ y,
+                                                       const __nv_bfloat16* __restrict__ res,
+                                                       const float* __restrict__ scale,
+                                                       const float* __restrict__ shift, __nv_bfloat16* __restrict__ z,
+                                                       long long nvec, int C8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % C8);
+    Vec8 v = load_bf16x8(y + i * 8);
+    Vec8 sc = load_f32x8(scale + cv * 8), sh = load_f32x8(shift + cv * 8);
+    Vec8 o;
+    if (RES) {
+      Vec8 rr = load_bf16x8(res + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.v[j] = fmaf(v.v[j], sc.v[j], sh.v[j]) + rr.v[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.v[j] = fmaf(v.v[j], sc.v[j], sh.v[j]);
+    }
+    if (RELU) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.v[j] = fmaxf(o.v[j], 0.f);
+    }
+    store_bf16x8(z + i * 8, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+// dz' = (dz_a [+ dz_b]) * (z > 0 if RELU).  Accumulates sum(dz') and sum(dz' * (y - mean)) per channel.
+template <bool RELU, bool TWO>
+__global__ void __launch_bounds__(kBnThreads)
+    bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
+                         const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ y,
+                         const float* __restrict__ mean, float* partial, long long M, int C, long long rows_per_blk) {
+  extern __shared__ float smem[];
+  const int C8 = C >> 3, RP = kBnThreads / C8;
+  const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+  const long long row0 = blockIdx.x * rows_per_blk;
+  const long long row1 = min(M, row0 + rows_per_blk);
+  if (r < RP) {
+    Vec8 mu = load_f32x8(mean + cv * 8);
+    for (long long row = row0 + r; row < row1; row += RP) {
+      const long long off = row * C + cv * 8;
+      Vec8 g = load_bf16x8(dza + off);
+      if (TWO) {
+        Vec8 g2 = load_bf16x8(dzb + off);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g.v[j] += g2.v[j];
+      }
+      if (RELU) {
+        Vec8 zz = load_bf16x8(z + off);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+      }
+      Vec8 yy = load_bf16x8(y + off);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        acc[0][j] += g.v[j];
+        acc[1][j] += g.v[j] * (yy.v[j] - mu.v[j]);
+      }
+    }
+    block_reduce_store<2>(acc, smem, partial, C, C8, RP, cv, r, C);
+  } else {
+    __syncthreads();
+  }
+}
+
+// partials -> dgamma/dbeta (fp32, optionally accumulated into existing grads) and the three per-channel
+// coefficients of  dy = k1*dz' + k2*y + k3.  With world > 1 the two sums are reduced across GPUs in-kernel.
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
+                                       const float* __restrict__ gamma, const float* __restrict__ mean,
+                                       const float* __restrict__ invstd, float* dgamma, float* dbeta, int accumulate,
+                                       float* coef, XgpuCtx xg, int slot_off) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  float sdy = 0.f, sdx = 0.f;
+  if (c < C) {
+    for (int b = 0; b < nblk; ++b) {
+      sdy += partial[(size_t)b * 2 * C + c];
+      sdx += partial[(size_t)b * 2 * C + C + c];
+    }
+  }
+  // Local sums give this rank's dgamma/dbeta (DDP averages them later, as torch's SyncBatchNorm does).
+  const float sdy_local = sdy, sdx_local = sdx;
+  float total = count;
+  if (xg.world > 1) {
+    float* mine = xg.data[xg.rank] + slot_off;
+    if (c < C) {
+      mine[c] = sdy;
+      mine[C + c] = sdx;
+    }
+    if (c == 0) mine[2 * C] = count;
+    xgpu_barrier(xg, blockIdx.x);
+    sdy = 0.f; sdx = 0.f; total = 0.f;
+    for (int rk = 0; rk < xg.world; ++rk) {
+      const float* peer = xg.data[rk] + slot_off;
+      if (c < C) {
+        sdy += ld_relaxed_sys_f32(peer + c);
+        sdx += ld_relaxed_sys_f32(peer + C + c);
+      }
+      total += ld_relaxed_sys_f32(peer + 2 * C);
+    }
+    xgpu_barrier(xg, blockIdx.x);
+  }
+  if (c >= C) return;
+  const float is = invstd[c], mu = mean[c], g = gamma[c];
+  const float dg = sdx_local * is, db = sdy_local;
+  if (dgamma) dgamma[c] = accumulate ? dgamma[c] + dg : dg;
+  if (dbeta) dbeta[c] = accumulate ? dbeta[c] + db : db;
+  const float A = g * is;
+  const float k2 = -A * is * is * sdx / total;
+  coef[c] = A;
+  coef[C + c] = k2;
+  coef[2 * C + c] = -A * sdy / total - k2 * mu;
+}
+
+// dy = k1*dz' + k2*y + k3 ; optionally also emits dz' (the gradient that flows into the residual branch).
+template <bool RELU, bool TWO, bool DRES>
+__global__ void __launch_bounds__(256)
+    bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
+                        const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ y,
+                        const float* __restrict__ coef, __nv_bfloat16* __restrict__ dy,
+                        __nv_bfloat16* __restrict__ dres, long long nvec, int C8) {
+  const int C = C8 * 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % C8);
+    Vec8 g = load_bf16x8(dza + i * 8);
+    if (TWO) {
+      Vec8 g2 = load_bf16x8(dzb + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g.v[j] += g2.v[j];
+    }
+    if (RELU) {
+      Vec8 zz = load_bf16x8(z + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+    }
+    if (DRES) store_bf16x8(dres + i * 8, g);
+    Vec8 yy = load_bf16x8(y + i * 8);
+    Vec8 k1 = load_f32x8(coef + cv * 8), k2 = load_f32x8(coef + C + cv * 8), k3 = load_f32x8(coef + 2 * C + cv * 8);
+    Vec8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = fmaf(k1.v[j], g.v[j], fmaf(k2.v[j], yy.v[j], k3.v[j]));
+    store_bf16x8(dy + i * 8, o);
+  }
+}
+
+static int plan_blocks(long long M, int C, long long* rows_per_blk) {
+  const int C8 = C / 8, RP = kBnThreads / C8;
+  long long nblk = (M + (long long)RP * 8 - 1) / ((long long)RP * 8);
+  if (nblk > kMaxPartialBlocks) nblk = kMaxPartialBlocks;
+  if (nblk < 1) nblk = 1;
+  long long rpb = (M + nblk - 1) / nblk;
+  rpb = (rpb + RP - 1) / RP * RP;
+  nblk = (M + rpb - 1) / rpb;
+  *rows_per_blk = rpb;
+  return (int)nblk;
+}
+
+static int stream_grid(long long nvec) {
+  long long b = (nvec + 255) / 256;
+  const long long cap = 148LL * 16;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartialBlocks * 2 * C; }
+
+static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }
+
+extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
+                               const float* beta, float* running_mean, float* running_var,
+                               long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
+                               float* invstd, float* scale_shift /*2C*/, float* partial, const b2_xgpu_ctx* xg,
+                               int xg_slot, void* stream) {
+  if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
+  cudaStream_t st = (cudaStream_t)stream;
+  long long rpb;
+  const int nblk = plan_blocks(M, C, &rpb);
+  const int RP = kBnThreads / (C / 8);
+  bn_stats_kernel<<<nblk, kBnThreads, 2 * RP * C * sizeof(float), st>>>((const __nv_bfloat16*)y, partial, M, C, rpb);
+  XgpuCtx ctx = xgpu_from_c(xg);
+  const int fthreads = 128;
+  bn_finalize_kernel<<<(C + fthreads - 1) / fthreads, fthreads, 0, st>>>(
+      partial, nblk, C, (float)M, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, mean,
+      invstd, scale_shift, scale_shift + C, ctx, xg_slot);
+  const long long nvec = M * (C / 8);
+  const int grid = stream_grid(nvec);
+  const __nv_bfloat16* yy = (const __nv_bfloat16*)y;
+  const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
+  __nv_bfloat16* zz = (__nv_bfloat16*)z;
+  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  return cudaGetLastError();
+}
+
+extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
+                              const float* beta, const float* running_mean, const float* running_var, float eps,
+                              int relu, float* scale_shift, void* stream) {
+  if (C % 8) return cudaErrorInvalidValue;
+  cudaStream_t st = (cudaStream_t)stream;
+  bn_eval_coeffs_kernel<<<(C + 127) / 128, 128, 0, st>>>(C, gamma, beta, running_mean, running_var, eps, scale_shift,
+                                                       scale_shift + C);
+  const long long nvec = M * (C / 8);
+  const int grid = stream_grid(nvec);
+  const __nv_bfloat16* yy = (const __nv_bfloat16*)y;
+  const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
+  __nv_bfloat16* zz = (__nv_bfloat16*)z;
+  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  return cudaGetLastError();
+}
+
+#define B2_BWD_DISPATCH(KERNEL, ...)                                            \
+  do {                                                                          \
+    if (relu) {                                                                 \
+      if (dzb) KERNEL(true, true, __VA_ARGS__); else KERNEL(true, false, __VA_ARGS__);   \
+    } else {                                                                    \
+      if (dzb) KERNEL(false, true, __VA_ARGS__); else KERNEL(false, false, __VA_ARGS__); \
+    }                                                                           \
+  } while (0)
+
+extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, void* dy, void* dres,
+                         long long M, int C, const float* gamma, const float* mean, const float* invstd,
+                         float* dgamma, float* dbeta, int accumulate, int relu, float* coef /*3C*/, float* partial,
+                         const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
+  cudaStream_t st = (cudaStream_t)stream;
+  long long rpb;
+  const int nblk = plan_blocks(M, C, &rpb);
+  const int RP = kBnThreads / (C / 8);
+  const size_t sm = 2 * RP * C * sizeof(float);
+  const __nv_bfloat16 *a = (const __nv_bfloat16*)dz_a, *b = (const __nv_bfloat16*)dz_b,
+                      *zz = (const __nv_bfloat16*)z, *yy = (const __nv_bfloat16*)y;
+  const bool dzb = dz_b != nullptr;
+#define RED(R, T, ...) bn_bwd_reduce_kernel<R, T><<<nblk, kBnThreads, sm, st>>>(a, b, zz, yy, mean, partial, M, C, rpb)
+  B2_BWD_DISPATCH(RED, 0);
+#undef RED
+  XgpuCtx ctx = xgpu_from_c(xg);
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nblk, C, (float)M, gamma, mean, invstd, dgamma,
+                                                          dbeta, accumulate, coef, ctx, xg_slot);
+  const long long nvec = M * (C / 8);
+  const int grid = stream_grid(nvec);
+  __nv_bfloat16 *dyp = (__nv_bfloat16*)dy, *drp = (__nv_bfloat16*)dres;
+#define APP(R, T, ...)                                                                                       \
+  do {                                                                                                       \
+    if (dres) bn_bwd_apply_kernel<R, T, true><<<grid, 256, 0, st>>>(a, b, zz, yy, coef, dyp, drp, nvec, C / 8); \
+    else bn_bwd_apply_kernel<R, T, false><<<grid, 256, 0, st>>>(a, b, zz, yy, coef, dyp, drp, nvec, C / 8);     \
+  } while (0)
+  B2_BWD_DISPATCH(APP, 0);
+#undef APP
+  return cudaGetLastError();
+}

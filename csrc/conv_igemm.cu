@@ -1,0 +1,469 @@
+// Implicit-GEMM convolution for sm_100a: tcgen05.mma with TMEM accumulators, weights (and 1x1 activations)
+// staged by TMA, im2col rows of k>1 / strided convolutions gathered by producer warps with zero-filling
+// cp.async straight into the 128B-swizzled UMMA layout.  One kernel template serves
+//   fprop : y[N*Ho*Wo, Cout]   = im2col(x)[.., taps*Cin]      * W[Cout, taps*Cin]^T     (A K-major, B K-major)
+//   dgrad : dx[N*H*W, Cin]     = im2col_T(dy)[.., taps*Cout]  * W[(tap,Cout), Cin]      (A K-major, B MN-major)
+//   wgrad : dW[Cout, tap, Cin] = dy[pixels, Cout]^T           * im2col(x)[pixels, Cin]  (A MN-major, B MN-major)
+// Layouts: activations NHWC bf16, weights OHWI bf16 (== torch channels_last of an OIHW tensor), dW fp32 OHWI.
+//
+// Replaces cuDNN fprop/dgrad/wgrad used by the reference through torchvision's ResNet
+// (reference: resnet/main.py:76,121,123 -> aten::convolution / convolution_backward).
+#include "b200ddp.h"
+#include "ptx.cuh"
+#include "tmap.h"
+
+namespace b2 {
+
+enum ConvKind { FPROP = 0, DGRAD = 1, WGRAD = 2 };
+
+struct ConvParams {
+  // Gathered activation tensor (x for fprop/wgrad, dy for dgrad), NHWC bf16.
+  const __nv_bfloat16* src;
+  int srcH, srcW, srcC;
+  // Pixel grid that GEMM rows (fprop/dgrad: M rows; wgrad: K rows) enumerate: [N, rowH, rowW].
+  int rowH, rowW;
+  int KH, KW, stride, pad;
+  int M;        // GEMM M  (fprop/dgrad: pixels; wgrad: Cout)
+  int Ncols;    // GEMM N  (fprop: Cout; dgrad: Cin; wgrad: Cin)
+  int Kblocks;  // number of 64-wide k-blocks in total (wgrad: over all pixels)
+  int cpb;      // 64-channel blocks per tap of the K axis (fprop: Cin/64, dgrad: Cout/64); wgrad: unused
+  int Kpix;     // wgrad: number of pixels (K extent)
+  int splits;   // wgrad: split-K factor
+  int kb_per_split;
+  int tapC;     // channels per tap in the weight's K axis (= Cin): column offset of a tap in W2d
+  void* out;    // fprop/dgrad: bf16 [M, Ncols]; wgrad: fp32 workspace [splits][Cout][taps*Cin]
+  long long out_ld;
+  long long split_stride;  // wgrad: elements between split slabs
+};
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kGatherThreads = 128;
+constexpr int kThreads = 192;  // warps 0-3 gather + epilogue, warp 4 TMA, warp 5 MMA/TMEM
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 3 : 4);
+  // Gather warps publish a stage this many k-blocks after issuing its cp.asyncs (loads stay in flight).
+  static constexpr int kLag = kStages - 2;
+  static constexpr int kABytes = BM * 128;  // 16 KB either major-ness
+  static constexpr int kBBytes = BN * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// Decode a pixel index into (n, h, w) for a [*, PH, PW] grid.
+B2_DEVICE void decode_pix(int p, int PH, int PW, int& n, int& h, int& w) {
+  int hw = PH * PW;
+  n = p / hw;
+  int r = p - n * hw;
+  h = r / PW;
+  w = r - h * PW;
+}
+
+template <int KIND, bool GATHER, int BN>
+__global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
+    igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const ConvParams p) {
+  using C = Cfg<BN>;
+  constexpr int kLag = C::kLag;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* tmem_full = bars + 2 * C::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::kStages + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // Tile coordinates. x = N tile (fastest, so CTAs that share an A tile are co-scheduled), y = M tile.
+  const int n0 = blockIdx.x * BN;
+  const int m0 = blockIdx.y * BM;
+  int tap = 0, split = 0, kb_begin = 0, kb_end = p.Kblocks;
+  if (KIND == WGRAD) {
+    tap = blockIdx.z / p.splits;
+    split = blockIdx.z - tap * p.splits;
+    kb_begin = split * p.kb_per_split;
+    kb_end = min(p.Kblocks, kb_begin + p.kb_per_split);
+  }
+  const int nkb = kb_end - kb_begin;
+
+  // Which operand (if any) the gather warps fill: fprop/dgrad -> A, wgrad -> B.
+  constexpr bool kGatherA = GATHER && (KIND != WGRAD);
+  constexpr bool kGatherB = GATHER && (KIND == WGRAD);
+  constexpr uint32_t kTmaBytes = (kGatherA ? 0 : C::kABytes) + (kGatherB ? 0 : C::kBBytes);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1 + (GATHER ? kGatherThreads : 0));
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 5) tmem_alloc<BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ===================================================== TMA producer (one lane)
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int kb = kb_begin + i;
+        const int s = i % C::kStages;
+        const uint32_t ph = (i / C::kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* sA = smem + s * C::kStageBytes;
+        uint8_t* sB = sA + C::kABytes;
+        mbar_arrive_expect_tx(&full[s], kTmaBytes);
+        if (KIND == FPROP) {
+          if (!kGatherA) tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // x2d [M][Cin], box {64,128}
+          tma_load_2d(sB, &tmB, &full[s], kb * BK, n0);                 // W2d [Cout][K], box {64,BN}
+        } else if (KIND == DGRAD) {
+          if (!kGatherA) tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // dy2d [M][Cout], box {64,128}
+          const int t = kb / p.cpb, cob = kb - t * p.cpb;
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)  // W2d [Cout][taps*Cin], box {64 cin, 64 cout} -> MN-major B
+            tma_load_2d(sB + j * 8192, &tmB, &full[s], t * p.tapC + n0 + 64 * j, cob * 64);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 2; ++j)  // dy2d [pixels][Cout], box {64 cout, 64 pixels} -> MN-major A
+            tma_load_2d(sA + j * 8192, &tmA, &full[s], m0 + 64 * j, kb * BK);
+          if (!kGatherB) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)  // x2d [pixels][Cin]
+              tma_load_2d(sB + j * 8192, &tmB, &full[s], n0 + 64 * j, kb * BK);
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================================================== MMA issuer (one lane)
+    if (lane == 0) {
+      constexpr bool kAmn = (KIND == WGRAD);
+      constexpr bool kBmn = (KIND != FPROP);
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, kAmn, kBmn);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % C::kStages;
+        const uint32_t ph = (i / C::kStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t aBase = smem_u32(smem + s * C::kStageBytes);
+        const uint32_t bBase = aBase + C::kABytes;
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          // K-major: step 16 elements (32 B) inside the swizzle atom. MN-major: step 16 rows (2 KB).
+          const uint64_t da = kAmn ? make_smem_desc_sw128(aBase + k * 2048, 8192, 1024)
+                                   : make_smem_desc_sw128(aBase + k * 32, 16, 1024);
+          const uint64_t db = kBmn ? make_smem_desc_sw128(bBase + k * 2048, 8192, 1024)
+                                   : make_smem_desc_sw128(bBase + k * 32, 16, 1024);
+          umma_bf16(tmem_base, da, db, idesc, (i | k) != 0);
+        }
+        umma_commit(&empty[s]);  // smem slot reusable once these MMAs retire
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    // ===================================================== gather producers (warps 0-3)
+    if (GATHER) {
+      const int t = threadIdx.x;  // 0..127
+      const __nv_bfloat16* __restrict__ src = p.src;
+      if (KIND != WGRAD) {
+        // Row t of the A tile = output pixel m0+t for the whole tile.
+        const int m = m0 + t;
+        const bool row_ok = m < p.M;
+        int n, h, w;
+        decode_pix(row_ok ? m : 0, p.rowH, p.rowW, n, h, w);
+        const uint32_t swz = (t & 7);
+        int pending = 0;
+        for (int i = 0; i < nkb; ++i) {
+          const int kb = kb_begin + i;
+          const int s = i % C::kStages;
+          const uint32_t ph = (i / C::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
+          const int kh = tp / p.KW, kw = tp - kh * p.KW;
+          int sh, sw;
+          bool ok = row_ok;
+          if (KIND == FPROP) {
+            sh = h * p.stride - p.pad + kh;
+            sw = w * p.stride - p.pad + kw;
+          } else {  // DGRAD: dy pixel that tap (kh,kw) maps onto dx pixel (h,w), if any
+            const int th = h + p.pad - kh, tw = w + p.pad - kw;
+            ok = ok && th >= 0 && tw >= 0;
+            if (p.stride == 1) {
+              sh = th; sw = tw;
+            } else {
+              sh = th / p.stride; sw = tw / p.stride;
+              ok = ok && (sh * p.stride == th) && (sw * p.stride == tw);
+            }
+          }
+          ok = ok && sh >= 0 && sw >= 0 && sh < p.srcH && sw < p.srcW;
+          const __nv_bfloat16* g =
+              ok ? src + ((size_t)((n * p.srcH + sh) * p.srcW + sw) * p.srcC + cb * 64) : src;
+          const uint32_t dst = smem_u32(smem + s * C::kStageBytes) + t * 128;
+          const uint32_t nbytes = ok ? 16u : 0u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cp_async16(dst + ((j ^ swz) << 4), g + j * 8, nbytes);
+          cp_async_commit();
+          ++pending;
+          if (pending > kLag) {
+            cp_async_wait<kLag>();
+            fence_proxy_async_smem();
+            mbar_arrive(&full[(i - kLag) % C::kStages]);
+            --pending;
+          }
+        }
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        for (int i = nkb - pending; i < nkb; ++i) mbar_arrive(&full[i % C::kStages]);
+      } else {
+        // WGRAD: B tile rows are K (64 pixels per k-block); BN/64 channel blocks of 64.
+        constexpr int kItems = 64 * (BN / 64);
+        constexpr int kPer = (kItems + kGatherThreads - 1) / kGatherThreads;
+        const int kh = tap / p.KW, kw = tap - kh * p.KW;
+        int pending = 0;
+        for (int i = 0; i < nkb; ++i) {
+          const int kb = kb_begin + i;
+          const int s = i % C::kStages;
+          const uint32_t ph = (i / C::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          const uint32_t sB = smem_u32(smem + s * C::kStageBytes + C::kABytes);
+#pragma unroll
+          for (int q = 0; q < kPer; ++q) {
+            const int item = t + q * kGatherThreads;
+            if (item < kItems) {
+              const int r = item & 63, j = item >> 6;
+              const int pix = kb * BK + r;
+              bool ok = pix < p.Kpix;
+              int n, h, w;
+              decode_pix(ok ? pix : 0, p.rowH, p.rowW, n, h, w);
+              const int sh = h * p.stride - p.pad + kh, sw = w * p.stride - p.pad + kw;
+              ok = ok && sh >= 0 && sw >= 0 && sh < p.srcH && sw < p.srcW;
+              const __nv_bfloat16* g =
+                  ok ? src + ((size_t)((n * p.srcH + sh) * p.srcW + sw) * p.srcC + n0 + j * 64) : src;
+              const uint32_t dst = sB + j * 8192 + r * 128;
+              const uint32_t nbytes = ok ? 16u : 0u;
+              const uint32_t swz = r & 7;
+#pragma unroll
+              for (int c = 0; c < 8; ++c) cp_async16(dst + ((c ^ swz) << 4), g + c * 8, nbytes);
+            }
+          }
+          cp_async_commit();
+          ++pending;
+          if (pending > kLag) {
+            cp_async_wait<kLag>();
+            fence_proxy_async_smem();
+            mbar_arrive(&full[(i - kLag) % C::kStages]);
+            --pending;
+          }
+        }
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        for (int i = nkb - pending; i < nkb; ++i) mbar_arrive(&full[i % C::kStages]);
+      }
+    }
+
+    // ===================================================== epilogue (warps 0-3): TMEM -> regs -> global
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int row = warp * 32 + lane;  // accumulator row == TMEM lane
+    const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16);
+    if (KIND != WGRAD) {
+      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
+      const bool ok = (m0 + row) < p.M;
+      __nv_bfloat16* orow = out + (size_t)(m0 + row) * p.out_ld + n0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        if (ok) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+            o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+            o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+            o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+            st_v4(orow + c * 32 + q * 8, o);
+          }
+        }
+      }
+    } else {
+      float* out = reinterpret_cast<float*>(p.out) + (size_t)split * p.split_stride;
+      const bool ok = (m0 + row) < p.M;
+      float* orow = out + (size_t)(m0 + row) * p.out_ld + (size_t)tap * p.tapC + n0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        if (ok) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_free<BN>(tmem_base);
+}
+
+// dW[i] = (accumulate ? dW[i] : 0) + sum_s ws[s][i]   (fixed order -> deterministic)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, long long n, int splits,
+                                    long long split_stride, int accumulate) {
+  long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  float4 acc = accumulate ? *reinterpret_cast<const float4*>(dw + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int s = 0; s < splits; ++s) {
+    float4 v = *reinterpret_cast<const float4*>(ws + s * split_stride + i);
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  *reinterpret_cast<float4*>(dw + i) = acc;
+}
+
+template <int KIND, bool GATHER, int BN>
+static cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, dim3 grid,
+                          cudaStream_t st) {
+  auto kern = igemm_kernel<KIND, GATHER, BN>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  kern<<<grid, kThreads, Cfg<BN>::kSmem, st>>>(tmA, tmB, p);
+  return cudaGetLastError();
+}
+
+template <int KIND, bool GATHER>
+static cudaError_t launch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, dim3 grid,
+                             cudaStream_t st) {
+  switch (bn) {
+    case 64: return launch<KIND, GATHER, 64>(tmA, tmB, p, grid, st);
+    case 128: return launch<KIND, GATHER, 128>(tmA, tmB, p, grid, st);
+    case 256: return launch<KIND, GATHER, 256>(tmA, tmB, p, grid, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+static int pick_bn(int ncols, int force) {
+  if (force == 64 || force == 128 || force == 256) return (ncols % force == 0) ? force : 64;
+  if (ncols % 128 == 0) return 128;
+  return 64;
+}
+
+static int g_force_bn = 0;
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
+
+extern "C" int b2_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH,
+                             int KW, int stride, int pad, void* stream) {
+  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+  const int M = N * Ho * Wo, K = KH * KW * Cin;
+  const int bn = pick_bn(Cout, g_force_bn);
+  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  CUtensorMap tmA, tmB;
+  int e;
+  // A: x2d [M][Cin] (only dereferenced on the pure-GEMM path); B: W2d [Cout][K], box {64, bn}
+  if ((e = make_tmap_2d_bf16(&tmA, x, (uint64_t)Cin, (uint64_t)(gather ? N * H * W : M), 64, 128))) return e;
+  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)K, (uint64_t)Cout, 64, bn))) return e;
+  ConvParams p{};
+  p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
+  p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.M = M; p.Ncols = Cout; p.Kblocks = K / 64; p.cpb = Cin / 64; p.tapC = Cin;
+  p.out = y; p.out_ld = Cout; p.splits = 1;
+  dim3 grid(Cout / bn, (M + BM - 1) / BM, 1);
+  cudaStream_t st = (cudaStream_t)stream;
+  return gather ? launch_bn<FPROP, true>(bn, tmA, tmB, p, grid, st) : launch_bn<FPROP, false>(bn, tmA, tmB, p, grid, st);
+}
+
+extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                             int KW, int stride, int pad, void* stream) {
+  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+  const int M = N * H * W, K = KH * KW * Cout;
+  const int bn = pick_bn(Cin, g_force_bn);
+  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  CUtensorMap tmA, tmB;
+  int e;
+  if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) return e;
+  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) return e;
+  ConvParams p{};
+  p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
+  p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.M = M; p.Ncols = Cin; p.Kblocks = K / 64; p.cpb = Cout / 64; p.tapC = Cin;
+  p.out = dx; p.out_ld = Cin; p.splits = 1;
+  dim3 grid(Cin / bn, (M + BM - 1) / BM, 1);
+  cudaStream_t st = (cudaStream_t)stream;
+  return gather ? launch_bn<DGRAD, true>(bn, tmA, tmB, p, grid, st) : launch_bn<DGRAD, false>(bn, tmA, tmB, p, grid, st);
+}
+
+// Split-K plan for wgrad: enough CTAs for ~2 waves of 148 SMs x 2 resident CTAs, bounded by the workspace.
+extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes) {
+  const long long kpix = (long long)N * Ho * Wo;
+  const int kblocks = (int)((kpix + 63) / 64);
+  const int bn = pick_bn(Cin, g_force_bn);
+  const long long tiles = (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
+  long long want = (4 * 148 + tiles - 1) / tiles;
+  const long long wbytes = (long long)Cout * taps * Cin * 4;
+  long long cap = ws_bytes / wbytes;
+  if (want > cap) want = cap;
+  if (want > kblocks) want = kblocks;
+  if (want < 1) want = 1;
+  const int per = (int)((kblocks + want - 1) / want);
+  return (kblocks + per - 1) / per;
+}
+
+extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N,
+                             int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int accumulate,
+                             void* stream) {
+  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+  const int taps = KH * KW;
+  const long long kpix = (long long)N * Ho * Wo;
+  const int kblocks = (int)((kpix + 63) / 64);
+  const int bn = pick_bn(Cin, g_force_bn);
+  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  const long long wcount = (long long)Cout * taps * Cin;
+  if (ws_bytes < wcount * 4) return cudaErrorInvalidValue;
+  const int splits = b2_conv_wgrad_splits(N, Ho, Wo, Cin, Cout, taps, ws_bytes);
+  const int per = (kblocks + splits - 1) / splits;
+  CUtensorMap tmA, tmB;
+  int e;
+  if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, 64))) return e;
+  if ((e = make_tmap_2d_bf16(&tmB, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 64))) return e;
+  ConvParams p{};
+  p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
+  p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.M = Cout; p.Ncols = Cin; p.Kblocks = kblocks; p.Kpix = (int)kpix; p.tapC = Cin;
+  p.splits = splits; p.kb_per_split = per;
+  p.out = workspace; p.out_ld = (long long)taps * Cin; p.split_stride = wcount;
+  dim3 grid(Cin / bn, (Cout + BM - 1) / BM, taps * splits);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t ce = gather ? launch_bn<WGRAD, true>(bn, tmA, tmB, p, grid, st)
+                          : launch_bn<WGRAD, false>(bn, tmA, tmB, p, grid, st);
+  if (ce != cudaSuccess) return ce;
+  const int thr = 256;
+  const long long nvec = (wcount + 3) / 4;
+  wgrad_reduce_kernel<<<(unsigned)((nvec + thr - 1) / thr), thr, 0, st>>>(workspace, dw, wcount, splits, wcount,
+                                                                          accumulate);
+  return cudaGetLastError();
+}

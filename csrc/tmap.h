@@ -1,0 +1,12 @@
+// Host-side TMA descriptor construction. The driver entry point is resolved at run time through the
+// CUDA runtime, so the library has no link-time dependency on libcuda (it must load on CPU-only boxes).
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+
+namespace b2 {
+// Row-major bf16 matrix [outer][inner], 128B swizzle, zero fill for out-of-bounds boxes.
+// Returns 0 on success, a CUresult/cudaError value otherwise.
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint32_t box_inner,
+                      uint32_t box_outer);
+}  // namespace b2

@@ -1,0 +1,92 @@
+"""Convolution on the tcgen05 implicit-GEMM kernels (csrc/conv_igemm.cu) with a torch oracle path.
+
+Stands in for ``aten::convolution`` / ``convolution_backward`` that the reference reaches through
+torchvision's ResNet (reference resnet/main.py:76,121,123).  Activations are bf16 NHWC (torch
+``channels_last``), weights bf16 OHWI (``channels_last`` of the OIHW parameter), weight gradients fp32 OHWI.
+"""
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+_WS = {}
+_WS_BYTES = 256 << 20
+
+
+def workspace(device):
+    """Per-device split-K scratch for wgrad (allocated once, reused by every layer)."""
+    ws = _WS.get(device)
+    if ws is None:
+        ws = torch.empty(_WS_BYTES // 4, dtype=torch.float32, device=device)
+        _WS[device] = ws
+    return ws
+
+
+def _geom(x, w, stride, pad):
+    N, Cin, H, W = x.shape
+    Cout, _, KH, KW = w.shape
+    return N, H, W, Cin, Cout, KH, KW, stride, pad
+
+
+def _is_cl(t):
+    return t.is_contiguous(memory_format=torch.channels_last)
+
+
+def native_ok(x, w):
+    return (_lib.use_native(x) and x.dtype == torch.bfloat16 and x.shape[1] % 64 == 0 and w.shape[0] % 64 == 0)
+
+
+def conv_fprop(x, w, stride, pad):
+    """x: [N,Cin,H,W] bf16 channels_last; w: [Cout,Cin,KH,KW] bf16 channels_last -> y bf16 channels_last."""
+    N, H, W, Cin, Cout, KH, KW, s, p = _geom(x, w, stride, pad)
+    Ho, Wo = (H + 2 * p - KH) // s + 1, (W + 2 * p - KW) // s + 1
+    assert _is_cl(x) and _is_cl(w), "conv_fprop expects channels_last operands"
+    y = torch.empty((N, Cout, Ho, Wo), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    e = _lib.lib().b2_conv_fprop(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), N, H, W, Cin, Cout, KH, KW, s, p,
+                                 _lib.stream_ptr())
+    _lib.check(e, "b2_conv_fprop")
+    _lib.count_launch()
+    return y
+
+
+def conv_dgrad(dy, w, x_shape, stride, pad):
+    N, Cin, H, W = x_shape
+    Cout, _, KH, KW = w.shape
+    assert _is_cl(dy) and _is_cl(w)
+    dx = torch.empty((N, Cin, H, W), dtype=torch.bfloat16, device=dy.device, memory_format=torch.channels_last)
+    e = _lib.lib().b2_conv_dgrad(_lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), N, H, W, Cin, Cout, KH, KW, stride, pad,
+                                 _lib.stream_ptr())
+    _lib.check(e, "b2_conv_dgrad")
+    _lib.count_launch()
+    return dx
+
+
+def conv_wgrad(x, dy, w_shape, stride, pad, out=None, accumulate=False):
+    """Returns (or fills ``out``, e.g. a gradient-bucket slot) the fp32 OHWI weight gradient."""
+    N, Cin, H, W = x.shape
+    Cout, _, KH, KW = w_shape
+    assert _is_cl(x) and _is_cl(dy)
+    if out is None:
+        out = torch.empty(w_shape, dtype=torch.float32, device=x.device).contiguous(
+            memory_format=torch.channels_last)
+        accumulate = False
+    ws = workspace(x.device)
+    e = _lib.lib().b2_conv_wgrad(_lib.ptr(x), _lib.ptr(dy), _lib.ptr(out), _lib.ptr(ws),
+                                 _lib.c_ll(ws.numel() * 4), N, H, W, Cin, Cout, KH, KW, stride, pad,
+                                 int(accumulate), _lib.stream_ptr())
+    _lib.check(e, "b2_conv_wgrad")
+    _lib.count_launch(2)
+    return out
+
+
+# ------------------------------------------------------------------------------------------ torch oracle
+def ref_fprop(x, w, stride, pad):
+    return F.conv2d(x, w, None, stride, pad)
+
+
+def ref_dgrad(dy, w, x_shape, stride, pad):
+    return torch.nn.grad.conv2d_input(x_shape, w, dy, stride, pad)
+
+
+def ref_wgrad(x, dy, w_shape, stride, pad):
+    return torch.nn.grad.conv2d_weight(x, w_shape, dy, stride, pad)

@@ -1,0 +1,94 @@
+"""GPU check of the tcgen05 implicit-GEMM conv kernels against an fp32 torch reference, shape by shape.
+Each (kind, shape) prints one line; a CUDA fault in one kind does not hide the others (use --kind and run
+each in its own process).  Usage: python tools/conv_check.py --kind fprop|dgrad|wgrad [--batch 8] [--bn 0]
+"""
+import argparse
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from pytorch_distributed_tutorials_b200.ops import _lib, conv  # noqa: E402
+
+# (Cin, Cout, k, stride, pad, H)  -- ResNet-50 @224 and ResNet-18 @32 shapes with Cin % 64 == 0
+SHAPES = [
+    (64, 64, 1, 1, 0, 56), (64, 64, 3, 1, 1, 56), (64, 256, 1, 1, 0, 56), (256, 64, 1, 1, 0, 56),
+    (256, 128, 1, 1, 0, 56), (128, 128, 3, 2, 1, 56), (128, 512, 1, 1, 0, 28), (256, 512, 1, 2, 0, 56),
+    (512, 128, 1, 1, 0, 28), (128, 128, 3, 1, 1, 28), (512, 256, 1, 1, 0, 28), (256, 256, 3, 2, 1, 28),
+    (256, 1024, 1, 1, 0, 14), (512, 1024, 1, 2, 0, 28), (1024, 256, 1, 1, 0, 14), (256, 256, 3, 1, 1, 14),
+    (1024, 512, 1, 1, 0, 14), (512, 512, 3, 2, 1, 14), (512, 2048, 1, 1, 0, 7), (1024, 2048, 1, 2, 0, 14),
+    (2048, 512, 1, 1, 0, 7), (512, 512, 3, 1, 1, 7),
+    # ResNet-18 @32 (CIFAR): tiny spatial extents
+    (64, 64, 3, 1, 1, 8), (64, 128, 3, 2, 1, 8), (128, 128, 3, 1, 1, 4), (64, 128, 1, 2, 0, 8),
+    (256, 256, 3, 1, 1, 2), (512, 512, 3, 1, 1, 1), (256, 512, 1, 2, 0, 2),
+]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--kind", default="fprop")
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--bn", type=int, default=0)
+    ap.add_argument("--limit", type=int, default=0)
+    ap.add_argument("--time", action="store_true")
+    a = ap.parse_args()
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    _lib.lib().b2_conv_set_tile_n(a.bn)
+    shapes = SHAPES[: a.limit] if a.limit else SHAPES
+    bad = 0
+    for (ci, co, k, s, p, H) in shapes:
+        N = a.batch
+        x = torch.randn(N, ci, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(co, ci, k, k, device=dev) * (1.0 / (ci * k * k) ** 0.5)).to(torch.bfloat16).contiguous(
+            memory_format=torch.channels_last)
+        Ho = (H + 2 * p - k) // s + 1
+        dy = torch.randn(N, co, Ho, Ho, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        xf, wf, dyf = x.float(), w.float(), dy.float()
+        try:
+            if a.kind == "fprop":
+                got = conv.conv_fprop(x, w, s, p).float()
+                ref = conv.ref_fprop(xf, wf, s, p)
+            elif a.kind == "dgrad":
+                got = conv.conv_dgrad(dy, w, x.shape, s, p).float()
+                ref = conv.ref_dgrad(dyf, wf, x.shape, s, p)
+            else:
+                got = conv.conv_wgrad(x, dy, w.shape, s, p).float()
+                ref = conv.ref_wgrad(xf, dyf, w.shape, s, p)
+            torch.cuda.synchronize()
+            err = (got - ref).abs().max().item()
+            scale = ref.abs().max().item() + 1e-6
+            rel = err / scale
+            cos = torch.nn.functional.cosine_similarity(got.flatten(), ref.flatten(), dim=0).item()
+            ok = rel < 2e-2
+            bad += (not ok)
+            ms = ""
+            if a.time and ok:
+                fn = {"fprop": lambda: conv.conv_fprop(x, w, s, p),
+                      "dgrad": lambda: conv.conv_dgrad(dy, w, x.shape, s, p),
+                      "wgrad": lambda: conv.conv_wgrad(x, dy, w.shape, s, p)}[a.kind]
+                for _ in range(3):
+                    fn()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(10):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                t = e0.elapsed_time(e1) / 10
+                fl = 2.0 * N * Ho * Ho * co * ci * k * k
+                ms = " %.3f ms %.1f TF/s" % (t, fl / t / 1e9)
+            print("%s %-5s ci=%4d co=%4d k=%d s=%d H=%3d N=%d  maxerr=%.4g rel=%.3g cos=%.5f%s" %
+                  ("OK  " if ok else "FAIL", a.kind, ci, co, k, s, H, N, err, rel, cos, ms), flush=True)
+        except Exception as e:  # noqa: BLE001
+            print("EXC  %s ci=%d co=%d k=%d s=%d H=%d: %r" % (a.kind, ci, co, k, s, H, e), flush=True)
+            bad += 1
+            break
+    print("%s: %d/%d failed" % (a.kind, bad, len(shapes)))
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
