@@ -1,0 +1,252 @@
+// Gradient all-reduce and broadcast over peer-mapped (symmetric) memory, fused with the 1/world scale and the
+// SGD-momentum update.  Kernels read and write other GPUs' bucket buffers directly over NVLink 5 / NVSwitch;
+// NCCL is never called.
+//
+//   one-shot : every rank reads the whole bucket from every peer and reduces locally (latency-bound sizes)
+//   two-shot : reduce-scatter by peer reads of the rank's own 1/W slice (written back in place), then an
+//              all-gather by peer reads of every owner's reduced slice, with the SGD update applied on the fly
+//   multimem : NVLS path (multimem.ld_reduce / multimem.st through a multicast mapping), when one is bound
+//   broadcast: peers pull a region of the source rank's window (parameter / BN-buffer sync)
+//
+// Reductions run in fixed rank order, so results are bit-identical on every rank and run to run.
+// Replaces ProcessGroupNCCL allreduce/broadcast used by DDP's Reducer and the foreach SGD step of the reference
+// (reference resnet/main.py:74,80,123,124).
+#include "b200ddp.h"
+#include "ptx.cuh"
+#include "xgpu.cuh"
+
+namespace b2 {
+
+constexpr int kArThreads = 512;
+constexpr int kOneShotMaxVecPerThread = 8;
+
+struct SgdArgs {
+  float* p32;                 // nullptr -> reduce only
+  float* mom;
+  __nv_bfloat16* shadow;
+  float lr, mu, wd;
+  int first;
+};
+
+B2_DEVICE float4 ld_peer_f4(const float* p) {
+  uint4 u = ld_volatile_v4(p);
+  return make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z), __uint_as_float(u.w));
+}
+B2_DEVICE void st_f4(float* p, float4 v) {
+  st_v4(p, make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)));
+}
+
+// g' = g + wd*p ; buf = first ? g' : mu*buf + g' ; p -= lr*buf ; shadow = bf16(p)      (4 elements)
+B2_DEVICE void sgd_apply4(const SgdArgs& a, long long vi, float4 g) {
+  float4 pp = reinterpret_cast<float4*>(a.p32)[vi];
+  float4 bb = a.first ? make_float4(0.f, 0.f, 0.f, 0.f) : reinterpret_cast<float4*>(a.mom)[vi];
+  const float gx = fmaf(a.wd, pp.x, g.x), gy = fmaf(a.wd, pp.y, g.y), gz = fmaf(a.wd, pp.z, g.z),
+              gw = fmaf(a.wd, pp.w, g.w);
+  bb.x = a.first ? gx : fmaf(a.mu, bb.x, gx); bb.y = a.first ? gy : fmaf(a.mu, bb.y, gy);
+  bb.z = a.first ? gz : fmaf(a.mu, bb.z, gz); bb.w = a.first ? gw : fmaf(a.mu, bb.w, gw);
+  pp.x -= a.lr * bb.x; pp.y -= a.lr * bb.y; pp.z -= a.lr * bb.z; pp.w -= a.lr * bb.w;
+  reinterpret_cast<float4*>(a.p32)[vi] = pp;
+  reinterpret_cast<float4*>(a.mom)[vi] = bb;
+  if (a.shadow) {
+    uint2 s;
+    s.x = pack_bf16x2(pp.x, pp.y); s.y = pack_bf16x2(pp.z, pp.w);
+    reinterpret_cast<uint2*>(a.shadow)[vi] = s;
+  }
+}
+
+B2_DEVICE float4 reduce_peers(const XgpuCtx& xg, long long off_f, long long vi, float scale) {
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < B2_MAX_WORLD; ++r) {
+    if (r < xg.world) {
+      const float4 v = ld_peer_f4(xg.data[r] + off_f + vi * 4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+  return acc;
+}
+
+// ------------------------------------------------------------------------------------------------ one-shot
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_oneshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd, int write_grad) {
+  xgpu_barrier(xg, blockIdx.x);
+  float4 keep[kOneShotMaxVecPerThread];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < kOneShotMaxVecPerThread; ++k) {
+    const long long vi = v0 + k * stride;
+    if (vi < nvec) {
+      keep[k] = reduce_peers(xg, off_f, vi, scale);
+      if (sgd.p32) sgd_apply4(sgd, vi, keep[k]);
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);  // every peer has finished reading this rank's raw gradients
+  if (write_grad) {
+    float* mine = xg.data[xg.rank] + off_f;
+#pragma unroll
+    for (int k = 0; k < kOneShotMaxVecPerThread; ++k) {
+      const long long vi = v0 + k * stride;
+      if (vi < nvec) st_f4(mine + vi * 4, keep[k]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ two-shot
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_twoshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd, int write_grad) {
+  const long long slice = (nvec + xg.world - 1) / xg.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  float* mine = xg.data[xg.rank] + off_f;
+
+  xgpu_barrier(xg, blockIdx.x);
+  {  // reduce-scatter: this rank owns [s0, s1)
+    const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
+    for (long long vi = s0 + t0; vi < s1; vi += stride) st_f4(mine + vi * 4, reduce_peers(xg, off_f, vi, scale));
+  }
+  xgpu_barrier(xg, blockIdx.x);
+  // all-gather (+ update): pull every owner's reduced slice; own slice is already local
+  for (int q = 0; q < xg.world; ++q) {
+    const int owner = (xg.rank + q) % xg.world;  // start with the local slice, then stagger peers
+    const long long s0 = slice * owner, s1 = min(nvec, s0 + slice);
+    const float* src = xg.data[owner] + off_f;
+    for (long long vi = s0 + t0; vi < s1; vi += stride) {
+      const float4 g = ld_peer_f4(src + vi * 4);
+      if (sgd.p32) sgd_apply4(sgd, vi, g);
+      if (write_grad && owner != xg.rank) st_f4(mine + vi * 4, g);
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);  // peers are done reading this rank's slice before it is overwritten again
+}
+
+// ------------------------------------------------------------------------------------------------ NVLS multimem
+// mc: multicast mapping of the same window (all ranks' copies at once). ld_reduce pulls a switch-reduced value,
+// st pushes to every rank.
+B2_DEVICE float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+B2_DEVICE void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_multimem_kernel(XgpuCtx xg, float* mc_base, long long off_f, long long nvec, float scale, SgdArgs sgd) {
+  const long long slice = (nvec + xg.world - 1) / xg.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  float* mc = mc_base + off_f;
+  float* mine = xg.data[xg.rank] + off_f;
+  xgpu_barrier(xg, blockIdx.x);
+  {
+    const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
+    for (long long vi = s0 + t0; vi < s1; vi += stride) {
+      float4 g = multimem_ld_reduce_f4(mc + vi * 4);
+      g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
+      multimem_st_f4(mc + vi * 4, g);  // lands in every rank's buffer
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);
+  if (sgd.p32) {
+    for (long long vi = t0; vi < nvec; vi += stride) sgd_apply4(sgd, vi, ld_peer_f4(mine + vi * 4));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ broadcast
+__global__ void __launch_bounds__(kArThreads)
+    broadcast_kernel(XgpuCtx xg, long long off_bytes, long long nvec16, int src, uint4* dst_override) {
+  xgpu_barrier(xg, blockIdx.x);
+  if (xg.rank != src || dst_override) {
+    const uint4* s = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(xg.data[src]) + off_bytes);
+    uint4* d = dst_override ? dst_override
+                            : reinterpret_cast<uint4*>(reinterpret_cast<char*>(xg.data[xg.rank]) + off_bytes);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec16; i += stride)
+      st_v4(d + i, ld_volatile_v4(s + i));
+  }
+  xgpu_barrier(xg, blockIdx.x);
+}
+
+// Plain device-side barrier (one CTA per rank): orders everything before it on all ranks' streams.
+__global__ void barrier_kernel(XgpuCtx xg, int channel) { xgpu_barrier(xg, channel); }
+
+}  // namespace b2
+
+using namespace b2;
+
+static int clamp_blocks(int nblocks, long long nvec) {
+  long long need = (nvec + kArThreads - 1) / kArThreads;
+  if (nblocks <= 0) nblocks = 64;
+  if (nblocks > B2_XGPU_CHANNELS) nblocks = B2_XGPU_CHANNELS;
+  if (need < nblocks) nblocks = (int)(need < 1 ? 1 : need);
+  return nblocks;
+}
+
+extern "C" long long b2_allreduce_oneshot_max_elems(int nblocks) {
+  if (nblocks <= 0 || nblocks > B2_XGPU_CHANNELS) nblocks = B2_XGPU_CHANNELS;
+  return (long long)nblocks * kArThreads * kOneShotMaxVecPerThread * 4;
+}
+
+extern "C" int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long n, int algo,
+                            float scale, float* p32, float* mom, void* shadow_bf16, float lr, float momentum,
+                            float weight_decay, int first_step, int write_grad, int nblocks, void* stream) {
+  if (!ctx || n <= 0 || (n & 3) || (offset_bytes & 15)) return cudaErrorInvalidValue;
+  XgpuCtx xg = xgpu_from_c(ctx);
+  const long long nvec = n >> 2;
+  const long long off_f = offset_bytes >> 2;
+  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (algo == B2_AR_AUTO) {
+    // One-shot moves (W-1)*S inbound per GPU but has two barriers and no second pass: wins only when small.
+    algo = (n * 4 <= (512 << 10)) ? B2_AR_ONESHOT : B2_AR_TWOSHOT;
+    if (mc_base && n * 4 >= (1 << 20)) algo = B2_AR_MULTIMEM;
+  }
+  if (algo == B2_AR_ONESHOT) {
+    int nb = nblocks > 0 ? nblocks : B2_XGPU_CHANNELS;
+    if (nb > B2_XGPU_CHANNELS) nb = B2_XGPU_CHANNELS;
+    if (n > b2_allreduce_oneshot_max_elems(nb)) algo = B2_AR_TWOSHOT;
+    else {
+      // keep per-thread work balanced: as many blocks as needed for <= 8 vec4 per thread, at least 1
+      long long need = (nvec + (long long)kArThreads * kOneShotMaxVecPerThread - 1) /
+                       ((long long)kArThreads * kOneShotMaxVecPerThread);
+      long long spread = (nvec + kArThreads - 1) / kArThreads;
+      int b = (int)(spread < nb ? spread : nb);
+      if (b < need) b = (int)need;
+      if (b < 1) b = 1;
+      allreduce_oneshot_kernel<<<b, kArThreads, 0, st>>>(xg, off_f, nvec, scale, sgd, write_grad);
+      return cudaGetLastError();
+    }
+  }
+  if (algo == B2_AR_MULTIMEM) {
+    if (!mc_base) return cudaErrorInvalidValue;
+    allreduce_multimem_kernel<<<clamp_blocks(nblocks, nvec / xg.world + 1), kArThreads, 0, st>>>(
+        xg, (float*)mc_base, off_f, nvec, scale, sgd);
+    return cudaGetLastError();
+  }
+  allreduce_twoshot_kernel<<<clamp_blocks(nblocks, nvec / xg.world + 1), kArThreads, 0, st>>>(xg, off_f, nvec, scale,
+                                                                                             sgd, write_grad);
+  return cudaGetLastError();
+}
+
+extern "C" int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbytes, int src,
+                            void* dst_override, int nblocks, void* stream) {
+  if (!ctx || nbytes <= 0 || (nbytes & 15) || (offset_bytes & 15)) return cudaErrorInvalidValue;
+  XgpuCtx xg = xgpu_from_c(ctx);
+  const long long nvec = nbytes >> 4;
+  broadcast_kernel<<<clamp_blocks(nblocks, nvec), kArThreads, 0, (cudaStream_t)stream>>>(xg, offset_bytes, nvec, src,
+                                                                                        (uint4*)dst_override);
+  return cudaGetLastError();
+}
+
+extern "C" int b2_xgpu_barrier(const b2_xgpu_ctx* ctx, int channel, void* stream) {
+  if (!ctx) return cudaErrorInvalidValue;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(xgpu_from_c(ctx), channel);
+  return cudaGetLastError();
+}

@@ -104,7 +104,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblk, 
       mine[c] = s;
       mine[C + c] = ss;
     }
-    if (c == 0) mine[2 * C] = count;
+    if (threadIdx.x == 0) mine[2 * C + blockIdx.x] = count;
     xgpu_barrier(xg, /*channel=*/blockIdx.x);
     s = 0.f; ss = 0.f; total = 0.f;
     for (int rk = 0; rk < xg.world; ++rk) {
@@ -113,7 +113,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblk, 
         s += ld_relaxed_sys_f32(peer + c);
         ss += ld_relaxed_sys_f32(peer + C + c);
       }
-      total += ld_relaxed_sys_f32(peer + 2 * C);
+      total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
     }
     xgpu_barrier(xg, blockIdx.x);  // nobody overwrites its slot while a peer may still be reading it
   }
@@ -240,7 +240,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nb
       mine[c] = sdy;
       mine[C + c] = sdx;
     }
-    if (c == 0) mine[2 * C] = count;
+    if (threadIdx.x == 0) mine[2 * C + blockIdx.x] = count;
     xgpu_barrier(xg, blockIdx.x);
     sdy = 0.f; sdx = 0.f; total = 0.f;
     for (int rk = 0; rk < xg.world; ++rk) {
@@ -249,7 +249,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nb
         sdy += ld_relaxed_sys_f32(peer + c);
         sdx += ld_relaxed_sys_f32(peer + C + c);
       }
-      total += ld_relaxed_sys_f32(peer + 2 * C);
+      total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
     }
     xgpu_barrier(xg, blockIdx.x);
   }

@@ -31,6 +31,7 @@ struct ConvParams {
   int splits;   // wgrad: split-K factor
   int kb_per_split;
   int tapC;     // channels per tap in the weight's K axis (= Cin): column offset of a tap in W2d
+  const float* bias;  // fprop only, optional: added per output column (classifier)
   void* out;    // fprop/dgrad: bf16 [M, Ncols]; wgrad: fp32 workspace [splits][Cout][taps*Cin]
   long long out_ld;
   long long split_stride;  // wgrad: elements between split slabs
@@ -289,6 +290,13 @@ __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
         if (ok) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
+            const int col = n0 + c * 32 + q * 8;
+            if (col + 8 > p.Ncols) break;
+            if (p.bias) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
+            }
             uint4 o;
             o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
             o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
@@ -373,9 +381,9 @@ using namespace b2;
 
 extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
 
-extern "C" int b2_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH,
-                             int KW, int stride, int pad, void* stream) {
-  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
+                             int Cout, int KH, int KW, int stride, int pad, void* stream) {
+  if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * Ho * Wo, K = KH * KW * Cin;
   const int bn = pick_bn(Cout, g_force_bn);
@@ -389,17 +397,18 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, void* y, int N, int H
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cout; p.Kblocks = K / 64; p.cpb = Cin / 64; p.tapC = Cin;
-  p.out = y; p.out_ld = Cout; p.splits = 1;
-  dim3 grid(Cout / bn, (M + BM - 1) / BM, 1);
+  p.out = y; p.out_ld = Cout; p.splits = 1; p.bias = bias;
+  dim3 grid((Cout + bn - 1) / bn, (M + BM - 1) / BM, 1);
   cudaStream_t st = (cudaStream_t)stream;
   return gather ? launch_bn<FPROP, true>(bn, tmA, tmB, p, grid, st) : launch_bn<FPROP, false>(bn, tmA, tmB, p, grid, st);
 }
 
 extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
                              int KW, int stride, int pad, void* stream) {
-  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+  if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
-  const int M = N * H * W, K = KH * KW * Cout;
+  const int M = N * H * W;
+  const int cpb = (Cout + 63) / 64;
   const int bn = pick_bn(Cin, g_force_bn);
   const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
   CUtensorMap tmA, tmB;
@@ -409,7 +418,7 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   ConvParams p{};
   p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
   p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
-  p.M = M; p.Ncols = Cin; p.Kblocks = K / 64; p.cpb = Cout / 64; p.tapC = Cin;
+  p.M = M; p.Ncols = Cin; p.Kblocks = KH * KW * cpb; p.cpb = cpb; p.tapC = Cin;
   p.out = dx; p.out_ld = Cin; p.splits = 1;
   dim3 grid(Cin / bn, (M + BM - 1) / BM, 1);
   cudaStream_t st = (cudaStream_t)stream;
@@ -435,7 +444,7 @@ extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, in
 extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N,
                              int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int accumulate,
                              void* stream) {
-  if (Cin % 64 || Cout % 64) return cudaErrorInvalidValue;
+  if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int taps = KH * KW;
   const long long kpix = (long long)N * Ho * Wo;

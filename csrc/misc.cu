@@ -1,0 +1,417 @@
+// Pooling, loss, optimizer and stem helpers (all NHWC bf16 activations, fp32 master parameters).
+//   maxpool 3x3/2 fwd + bwd (deterministic gather form, first-max tie rule like aten::max_pool2d_with_indices)
+//   global average pool fwd + bwd
+//   cross-entropy (log-softmax + NLL, mean) fwd + bwd on bf16 logits, bias-gradient column sum
+//   SGD with momentum / weight decay on flat buffers, emitting the bf16 compute copy in the same pass
+//   stem 7x7/2 (3 input channels): im2col straight from the NCHW fp32/bf16 input batch, weight pack / unpack
+//
+// Reference: resnet/main.py:76 (torchvision maxpool/avgpool/fc), :102 (nn.CrossEntropyLoss), :103,:124 (optim.SGD).
+#include "b200ddp.h"
+#include "ptx.cuh"
+
+namespace b2 {
+
+B2_DEVICE void unpack8(uint4 u, float (&v)[8]) {
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+B2_DEVICE uint4 pack8(const float (&v)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  return u;
+}
+
+// ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                          __nv_bfloat16* __restrict__ y, int N, int H, int W, int C8,
+                                                          int Ho, int Wo) {
+  const long long total = (long long)N * Ho * Wo * C8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % C8);
+    long long pix = i / C8;
+    const int ow = (int)(pix % Wo); pix /= Wo;
+    const int oh = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int h = oh * 2 - 1 + kh;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int w = ow * 2 - 1 + kw;
+        if (w < 0 || w >= W) continue;
+        float v[8];
+        unpack8(*reinterpret_cast<const uint4*>(x + (((long long)(n * H + h) * W + w) * C8 + cv) * 8), v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], v[j]);
+      }
+    }
+    *reinterpret_cast<uint4*>(y + i * 8) = pack8(m);
+  }
+}
+
+// dx[h,w] = sum over the (<=4) windows containing (h,w) of (dy_a [+ dy_b])[window] * [argmax(window) == (h,w)].
+template <bool TWO>
+__global__ void __launch_bounds__(256)
+    maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dya,
+                       const __nv_bfloat16* __restrict__ dyb, __nv_bfloat16* __restrict__ dx, int N, int H, int W,
+                       int C8, int Ho, int Wo) {
+  const long long total = (long long)N * H * W * C8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % C8);
+    long long pix = i / C8;
+    const int w = (int)(pix % W); pix /= W;
+    const int h = (int)(pix % H);
+    const int n = (int)(pix / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    const int oh0 = h >> 1, oh1 = min(Ho - 1, (h + 1) >> 1);
+    const int ow0 = w >> 1, ow1 = min(Wo - 1, (w + 1) >> 1);
+    for (int oh = oh0; oh <= oh1; ++oh) {
+      for (int ow = ow0; ow <= ow1; ++ow) {
+        float best[8];
+        int arg[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = -1; }
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int hh = oh * 2 - 1 + kh;
+          if (hh < 0 || hh >= H) continue;
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int ww = ow * 2 - 1 + kw;
+            if (ww < 0 || ww >= W) continue;
+            float v[8];
+            unpack8(*reinterpret_cast<const uint4*>(x + (((long long)(n * H + hh) * W + ww) * C8 + cv) * 8), v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (v[j] > best[j] || arg[j] < 0) { best[j] = v[j]; arg[j] = hh * W + ww; }
+          }
+        }
+        const long long o = (((long long)(n * Ho + oh) * Wo + ow) * C8 + cv) * 8;
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(dya + o), g);
+        if (TWO) {
+          float g2[8];
+          unpack8(*reinterpret_cast<const uint4*>(dyb + o), g2);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += g2[j];
+        }
+        const int self = h * W + w;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += (arg[j] == self) ? g[j] : 0.f;
+      }
+    }
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ global avg pool
+__global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW,
+                                   int C8) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * C8) return;
+  const int cv = i % C8, n = i / C8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int p = 0; p < HW; ++p) {
+    float v[8];
+    unpack8(*reinterpret_cast<const uint4*>(x + (((long long)n * HW + p) * C8 + cv) * 8), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += v[j];
+  }
+  const float inv = 1.f / HW;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] *= inv;
+  *reinterpret_cast<uint4*>(y + (long long)i * 8) = pack8(acc);
+}
+__global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N,
+                                   int HW, int C8) {
+  const long long total = (long long)N * HW * C8;
+  const float inv = 1.f / HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % C8);
+    const int n = (int)(i / ((long long)HW * C8));
+    float v[8];
+    unpack8(*reinterpret_cast<const uint4*>(dy + ((long long)n * C8 + cv) * 8), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= inv;
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ cross entropy
+// One CTA per row. loss_row = logsumexp(logits) - logits[label]; also stores lse for the backward pass.
+__global__ void __launch_bounds__(128) ce_fwd_kernel(const __nv_bfloat16* __restrict__ logits,
+                                                     const long long* __restrict__ labels, float* lse,
+                                                     float* loss_row, int ncls, int ld) {
+  __shared__ float red[4];
+  const int row = blockIdx.x;
+  const __nv_bfloat16* lr = logits + (long long)row * ld;
+  float mx = -INFINITY;
+  for (int j = threadIdx.x; j < ncls; j += blockDim.x) mx = fmaxf(mx, __bfloat162float(lr[j]));
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+  __syncthreads();
+  float s = 0.f;
+  for (int j = threadIdx.x; j < ncls; j += blockDim.x) s += __expf(__bfloat162float(lr[j]) - mx);
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float l = mx + __logf(red[0] + red[1] + red[2] + red[3]);
+    lse[row] = l;
+    const long long lab = labels[row];
+    loss_row[row] = (lab >= 0 && lab < ncls) ? l - __bfloat162float(lr[lab]) : 0.f;
+  }
+}
+__global__ void ce_mean_kernel(const float* __restrict__ loss_row, float* loss, int rows) {
+  __shared__ float red[32];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) s += loss_row[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) *loss = v / rows;
+  }
+}
+// dlogits = (softmax - onehot) * gscale / rows   (gscale = upstream gradient of the mean loss, device scalar)
+__global__ void ce_bwd_kernel(const __nv_bfloat16* __restrict__ logits, const long long* __restrict__ labels,
+                              const float* __restrict__ lse, const float* __restrict__ gscale,
+                              __nv_bfloat16* __restrict__ dlogits, int rows, int ncls, int ld) {
+  const float g = (gscale ? *gscale : 1.f) / rows;
+  const long long total = (long long)rows * ncls;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int row = (int)(i / ncls), j = (int)(i - (long long)row * ncls);
+    const float p = __expf(__bfloat162float(logits[(long long)row * ld + j]) - lse[row]);
+    dlogits[(long long)row * ld + j] = __float2bfloat16((p - (labels[row] == j ? 1.f : 0.f)) * g);
+  }
+}
+// out[j] (+)= sum_rows m[row][j]   (bias gradient of the classifier)
+__global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ m, float* out, int rows, int cols, int ld,
+                                   int accumulate) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= cols) return;
+  float s = 0.f;
+  for (int r = 0; r < rows; ++r) s += __bfloat162float(m[(long long)r * ld + j]);
+  out[j] = accumulate ? out[j] + s : s;
+}
+
+// ------------------------------------------------------------------------------------------------ SGD (momentum, wd)
+// g' = g*gscale + wd*p ; buf = first ? g' : mu*buf + g' ; p -= lr*buf ; shadow = bf16(p)
+__global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                  float* __restrict__ buf, __nv_bfloat16* __restrict__ shadow,
+                                                  long long n, float lr, float mu, float wd, float gscale,
+                                                  int first) {
+  const long long nv = n >> 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    float4 gg = reinterpret_cast<const float4*>(g)[i];
+    float4 bb = first ? make_float4(0, 0, 0, 0) : reinterpret_cast<float4*>(buf)[i];
+    float gx = fmaf(wd, pp.x, gg.x * gscale), gy = fmaf(wd, pp.y, gg.y * gscale);
+    float gz = fmaf(wd, pp.z, gg.z * gscale), gw = fmaf(wd, pp.w, gg.w * gscale);
+    bb.x = first ? gx : fmaf(mu, bb.x, gx); bb.y = first ? gy : fmaf(mu, bb.y, gy);
+    bb.z = first ? gz : fmaf(mu, bb.z, gz); bb.w = first ? gw : fmaf(mu, bb.w, gw);
+    pp.x -= lr * bb.x; pp.y -= lr * bb.y; pp.z -= lr * bb.z; pp.w -= lr * bb.w;
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(buf)[i] = bb;
+    if (shadow) {
+      uint2 s;
+      s.x = pack_bf16x2(pp.x, pp.y); s.y = pack_bf16x2(pp.z, pp.w);
+      reinterpret_cast<uint2*>(shadow)[i] = s;
+    }
+  }
+  // tail (n not a multiple of 4)
+  const long long t0 = nv << 2;
+  const long long t = t0 + blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t < n) {
+    float pp = p[t];
+    const float gx = fmaf(wd, pp, g[t] * gscale);
+    const float bb = first ? gx : fmaf(mu, buf[t], gx);
+    pp -= lr * bb;
+    p[t] = pp; buf[t] = bb;
+    if (shadow) shadow[t] = __float2bfloat16(pp);
+  }
+}
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = __float2bfloat16(src[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ stem (7x7/2, Cin=3)
+// A[row][k], k = (kh*7+kw)*3 + c for k < 147, zero for 147 <= k < 192.  Reads the NCHW input batch directly.
+template <typename T>
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ A,
+                                                          int N, int H, int W, int Ho, int Wo) {
+  const long long total = (long long)N * Ho * Wo * 24;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int chunk = (int)(i % 24);
+    long long pix = i / 24;
+    const int ow = (int)(pix % Wo); pix /= Wo;
+    const int oh = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = chunk * 8 + j;
+      float val = 0.f;
+      if (k < 147) {
+        const int tap = k / 3, c = k - tap * 3;
+        const int kh = tap / 7, kw = tap - kh * 7;
+        const int h = oh * 2 - 3 + kh, w = ow * 2 - 3 + kw;
+        if (h >= 0 && h < H && w >= 0 && w < W) val = (float)x[((long long)(n * 3 + c) * H + h) * W + w];
+      }
+      v[j] = val;
+    }
+    *reinterpret_cast<uint4*>(A + i * 8) = pack8(v);
+  }
+}
+// fp32 OHWI [64][147] -> bf16 [64][192] zero padded
+__global__ void stem_pack_w_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int Cout) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Cout * 192) return;
+  const int o = i / 192, k = i - o * 192;
+  wp[i] = __float2bfloat16(k < 147 ? w[o * 147 + k] : 0.f);
+}
+// fp32 [64][192] -> fp32 OHWI [64][147]
+__global__ void stem_unpack_dw_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int Cout,
+                                      int accumulate) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Cout * 147) return;
+  const int o = i / 147, k = i - o * 147;
+  const float v = dwp[o * 192 + k];
+  dw[i] = accumulate ? dw[i] + v : v;
+}
+// NCHW (fp32 or bf16) -> NHWC bf16, generic C (used for inputs of non-stem models / tests)
+template <typename T>
+__global__ void nchw_to_nhwc_bf16_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int HW) {
+  const long long total = (long long)N * C * HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long r = i / C;
+    const int p = (int)(r % HW);
+    const int n = (int)(r / HW);
+    y[i] = __float2bfloat16((float)x[((long long)n * C + c) * HW + p]);
+  }
+}
+
+static int sgrid(long long n, int per = 256) {
+  long long b = (n + per - 1) / per;
+  const long long cap = 148LL * 16;
+  return (int)(b < 1 ? 1 : (b < cap ? b : cap));
+}
+
+}  // namespace b2
+
+using namespace b2;
+typedef __nv_bfloat16 bf16;
+
+extern "C" int b2_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  maxpool_fwd_kernel<<<sgrid((long long)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, (bf16*)y, N, H, W, C / 8, Ho, Wo);
+  return cudaGetLastError();
+}
+extern "C" int b2_maxpool_bwd(const void* x, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
+                              void* stream) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int grid = sgrid((long long)N * H * W * (C / 8));
+  if (dy_b)
+    maxpool_bwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (const bf16*)dy_a,
+                                                                      (const bf16*)dy_b, (bf16*)dx, N, H, W, C / 8, Ho, Wo);
+  else
+    maxpool_bwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (const bf16*)dy_a, nullptr,
+                                                                       (bf16*)dx, N, H, W, C / 8, Ho, Wo);
+  return cudaGetLastError();
+}
+extern "C" int b2_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const int n = N * (C / 8);
+  avgpool_fwd_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, N, HW, C / 8);
+  return cudaGetLastError();
+}
+extern "C" int b2_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+  if (C % 8) return cudaErrorInvalidValue;
+  avgpool_bwd_kernel<<<sgrid((long long)N * HW * (C / 8)), 256, 0, (cudaStream_t)stream>>>((const bf16*)dy, (bf16*)dx,
+                                                                                            N, HW, C / 8);
+  return cudaGetLastError();
+}
+extern "C" int b2_ce_fwd(const void* logits, const long long* labels, float* lse, float* loss_row, float* loss,
+                         int rows, int ncls, int ld, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  ce_fwd_kernel<<<rows, 128, 0, st>>>((const bf16*)logits, labels, lse, loss_row, ncls, ld);
+  ce_mean_kernel<<<1, 256, 0, st>>>(loss_row, loss, rows);
+  return cudaGetLastError();
+}
+extern "C" int b2_ce_bwd(const void* logits, const long long* labels, const float* lse, const float* gscale,
+                         void* dlogits, float* dbias, int accumulate_bias, int rows, int ncls, int ld, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  ce_bwd_kernel<<<sgrid((long long)rows * ncls), 256, 0, st>>>((const bf16*)logits, labels, lse, gscale,
+                                                                (bf16*)dlogits, rows, ncls, ld);
+  if (dbias)
+    colsum_bf16_kernel<<<(ncls + 127) / 128, 128, 0, st>>>((const bf16*)dlogits, dbias, rows, ncls, ld,
+                                                           accumulate_bias);
+  return cudaGetLastError();
+}
+extern "C" int b2_colsum_bf16(const void* m, float* out, int rows, int cols, int ld, int accumulate, void* stream) {
+  colsum_bf16_kernel<<<(cols + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const bf16*)m, out, rows, cols, ld,
+                                                                            accumulate);
+  return cudaGetLastError();
+}
+extern "C" int b2_sgd_step(float* p, const float* g, float* buf, void* shadow_bf16, long long n, float lr,
+                           float momentum, float weight_decay, float grad_scale, int first_step, void* stream) {
+  if (n <= 0) return 0;
+  sgd_kernel<<<sgrid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(p, g, buf, (bf16*)shadow_bf16, n, lr, momentum,
+                                                                   weight_decay, grad_scale, first_step);
+  return cudaGetLastError();
+}
+extern "C" int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {
+  if (n <= 0) return 0;
+  cast_f32_bf16_kernel<<<sgrid(n), 256, 0, (cudaStream_t)stream>>>(src, (bf16*)dst, n);
+  return cudaGetLastError();
+}
+extern "C" int b2_stem_im2col(const void* x, int x_is_bf16, void* A, int N, int H, int W, void* stream) {
+  const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
+  const int grid = sgrid((long long)N * Ho * Wo * 24);
+  if (x_is_bf16)
+    stem_im2col_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)A, N, H, W, Ho, Wo);
+  else
+    stem_im2col_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, (bf16*)A, N, H, W, Ho, Wo);
+  return cudaGetLastError();
+}
+extern "C" int b2_stem_pack_w(const float* w, void* wp, int Cout, void* stream) {
+  stem_pack_w_kernel<<<(Cout * 192 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)wp, Cout);
+  return cudaGetLastError();
+}
+extern "C" int b2_stem_unpack_dw(const float* dwp, float* dw, int Cout, int accumulate, void* stream) {
+  stem_unpack_dw_kernel<<<(Cout * 147 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dwp, dw, Cout, accumulate);
+  return cudaGetLastError();
+}
+extern "C" int b2_nchw_to_nhwc_bf16(const void* x, int x_is_bf16, void* y, int N, int C, int HW, void* stream) {
+  const int grid = sgrid((long long)N * C * HW);
+  if (x_is_bf16)
+    nchw_to_nhwc_bf16_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, N, C, HW);
+  else
+    nchw_to_nhwc_bf16_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, (bf16*)y, N, C, HW);
+  return cudaGetLastError();
+}

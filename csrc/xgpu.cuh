@@ -1,0 +1,66 @@
+// Cross-GPU context used inside kernels: peer-mapped data windows + signal pads of every rank (symmetric
+// memory set up by csrc/symm.cu) and a device-side barrier built on system-scope release/acquire flags with
+// monotonically increasing epochs (never reset, so CUDA-graph replays need no host bookkeeping).
+#pragma once
+#include "b200ddp.h"
+#include "ptx.cuh"
+
+namespace b2 {
+
+struct XgpuCtx {
+  int rank, world;
+  float* data[B2_MAX_WORLD];
+  uint32_t* flags[B2_MAX_WORLD];
+  uint32_t* epoch;
+};
+
+static inline XgpuCtx xgpu_from_c(const b2_xgpu_ctx* c) {
+  XgpuCtx x{};
+  if (!c) {
+    x.rank = 0;
+    x.world = 1;
+    return x;
+  }
+  x.rank = c->rank;
+  x.world = c->world;
+  for (int i = 0; i < B2_MAX_WORLD; ++i) {
+    x.data[i] = reinterpret_cast<float*>(c->data[i]);
+    x.flags[i] = reinterpret_cast<uint32_t*>(c->flags[i]);
+  }
+  x.epoch = reinterpret_cast<uint32_t*>(c->epoch);
+  return x;
+}
+
+B2_DEVICE float ld_relaxed_sys_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Barrier across the same-numbered CTA of every rank. Must be reached by all threads of the CTA.
+// Pad layout on rank r: flags[r][channel * B2_MAX_WORLD + src] = last epoch signalled by rank `src`.
+// Everything this CTA wrote before the call is visible to every peer CTA after it returns.
+B2_DEVICE void xgpu_barrier(const XgpuCtx& xg, int channel) {
+  __shared__ uint32_t s_epoch;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t e = xg.epoch[channel] + 1;
+    xg.epoch[channel] = e;
+    s_epoch = e;
+  }
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  if (threadIdx.x < xg.world) {
+    const int peer = threadIdx.x;
+    fence_acq_rel_sys();
+    st_release_sys(xg.flags[peer] + channel * B2_MAX_WORLD + xg.rank, e);
+    const uint32_t* mine = xg.flags[xg.rank] + channel * B2_MAX_WORLD + peer;
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+      if (++spins > B2_SPIN_LIMIT) __trap();
+    }
+  }
+  __syncthreads();
+}
+
+}  // namespace b2

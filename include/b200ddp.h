@@ -15,14 +15,29 @@
 extern "C" {
 #endif
 
+#define B2_MAX_WORLD 8
+#define B2_XGPU_CHANNELS 64
+
+/* Peer-memory context handed to kernels that talk to other GPUs (built by b2_symm_* below).
+ * data[r]/flags[r] are this process's mappings of rank r's symmetric window and signal pad;
+ * epoch is local device memory holding one counter per barrier channel.  world <= 1 or a NULL
+ * pointer means "single GPU" and no peer memory is touched. */
+typedef struct b2_xgpu_ctx {
+  int rank, world;
+  void* data[B2_MAX_WORLD];
+  void* flags[B2_MAX_WORLD];
+  void* epoch;
+} b2_xgpu_ctx;
+
 /* ------------------------------------------------------------------------------------------------
  * Convolution as implicit GEMM on tcgen05/TMEM (csrc/conv_igemm.cu).
  * Reference: resnet/main.py:76,121,123 (torchvision resnet -> cuDNN fprop / dgrad / wgrad).
  * x: NHWC bf16 [N,H,W,Cin]; w: OHWI bf16 [Cout,KH,KW,Cin]; y: NHWC bf16 [N,Ho,Wo,Cout]; dw: OHWI fp32.
- * Cin and Cout must be multiples of 64 (the 3-channel stem has its own kernels below).
+ * Cin must be a multiple of 64 and Cout of 8 (the classifier runs as a 1x1 conv with Cout=1000; the 3-channel
+ * stem goes through b2_stem_im2col and then these same kernels with Cin=192).
  * ---------------------------------------------------------------------------------------------- */
-int b2_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
-                  int stride, int pad, void* stream);
+int b2_conv_fprop(const void* x, const void* w, const float* bias /*nullable, fp32[Cout]*/, void* y, int N, int H,
+                  int W, int Cin, int Cout, int KH, int KW, int stride, int pad, void* stream);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.
@@ -32,6 +47,108 @@ int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, lo
 int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes);
 /* Debug/tuning: force the N tile (64/128/256); 0 = automatic. */
 void b2_conv_set_tile_n(int bn);
+
+/* ------------------------------------------------------------------------------------------------
+ * BatchNorm (+ReLU, +residual add) forward/backward on NHWC bf16, fp32 statistics (csrc/bn.cu).
+ * Reference: torchvision BasicBlock/Bottleneck bn/relu/add reached from resnet/main.py:76,121,123
+ * (aten::native_batch_norm[_backward], relu_, add_, threshold_backward); with xg->world > 1 the statistics
+ * are reduced across GPUs inside the finalize kernel (torch.nn.SyncBatchNorm's all_gather/all_reduce).
+ * y: conv output [M,C]; z: block output; partial: scratch of b2_bn_partial_floats(C) floats.
+ * ---------------------------------------------------------------------------------------------- */
+long long b2_bn_partial_floats(int C);
+int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
+                    const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                    float momentum, float eps, int relu, float* mean, float* invstd, float* scale_shift,
+                    float* partial, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
+int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma, const float* beta,
+                   const float* running_mean, const float* running_var, float eps, int relu, float* scale_shift,
+                   void* stream);
+/* dz' = (dz_a + dz_b) * relu_mask(z); dy = BN backward of dz'; dres (optional) receives dz'. */
+int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, void* dy, void* dres, long long M,
+              int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+              int accumulate, int relu, float* coef, float* partial, const b2_xgpu_ctx* xg, int xg_slot,
+              void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Pooling, loss, optimizer, stem helpers (csrc/misc.cu).
+ * Reference: resnet/main.py:76 (maxpool / avgpool / fc of torchvision resnet), :102 (CrossEntropyLoss),
+ * :103 and :124 (optim.SGD momentum 0.9, weight_decay 1e-5, step()).
+ * ---------------------------------------------------------------------------------------------- */
+int b2_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);            /* 3x3 / 2 / pad 1 */
+int b2_maxpool_bwd(const void* x, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
+                   void* stream);
+int b2_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int b2_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int b2_ce_fwd(const void* logits, const long long* labels, float* lse, float* loss_row, float* loss, int rows,
+              int ncls, int ld, void* stream);
+int b2_ce_bwd(const void* logits, const long long* labels, const float* lse, const float* gscale, void* dlogits,
+              float* dbias, int accumulate_bias, int rows, int ncls, int ld, void* stream);
+int b2_colsum_bf16(const void* m, float* out, int rows, int cols, int ld, int accumulate, void* stream);
+/* p, g, buf: flat fp32; shadow: optional bf16 copy of p refreshed in the same pass. */
+int b2_sgd_step(float* p, const float* g, float* buf, void* shadow_bf16, long long n, float lr, float momentum,
+                float weight_decay, float grad_scale, int first_step, void* stream);
+int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+int b2_stem_im2col(const void* x_nchw, int x_is_bf16, void* A, int N, int H, int W, void* stream);
+int b2_stem_pack_w(const float* w_ohwi, void* wp_bf16, int Cout, void* stream);
+int b2_stem_unpack_dw(const float* dwp, float* dw_ohwi, int Cout, int accumulate, void* stream);
+int b2_nchw_to_nhwc_bf16(const void* x, int x_is_bf16, void* y, int N, int C, int HW, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * DDP reducer core: bucket planner + ready/launch state machine (csrc/reducer.cpp, host only).
+ * Reference: resnet/main.py:80 (DistributedDataParallel -> c10d::Reducer, compute_bucket_assignment_by_size).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b2_reducer b2_reducer;
+int b2_plan_buckets(const long long* sizes_bytes, int n, long long first_cap_bytes, long long cap_bytes,
+                    int* bucket_of_param);
+b2_reducer* b2_reducer_create(int n_params, const int* bucket_of_param, int n_buckets);
+void b2_reducer_destroy(b2_reducer* r);
+void b2_reducer_reset(b2_reducer* r);
+int b2_reducer_mark_ready(b2_reducer* r, int idx, int* launch);
+int b2_reducer_unlaunched(const b2_reducer* r);
+long long b2_reducer_iterations(const b2_reducer* r);
+int b2_reducer_ready_order(const b2_reducer* r, int* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * Symmetric-memory runtime and watchdog (csrc/symm.cu).
+ * Reference: resnet/main.py:74 init_process_group("nccl") -> ProcessGroupNCCL communicator, buffer
+ * registration and watchdog thread.
+ * ---------------------------------------------------------------------------------------------- */
+int b2_ipc_alloc(long long bytes, void** dptr, unsigned char* handle64);
+int b2_ipc_open(const unsigned char* handle64, void** dptr);
+int b2_ipc_close(void* dptr);
+int b2_ipc_free(void* dptr);
+long long b2_vmm_round(long long bytes, int device, int world);
+int b2_vmm_multicast_supported(int device);
+int b2_vmm_alloc(long long bytes, int device, void** dptr, unsigned long long* handle, int* fd);
+int b2_vmm_import(int fd, long long bytes, int device, void** dptr);
+int b2_mc_create(long long bytes, int world, unsigned long long* mc_handle, int* fd);
+int b2_mc_import(int fd, unsigned long long* mc_handle);
+int b2_mc_add_device(unsigned long long mc_handle, int device);
+int b2_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_handle, long long bytes, int device,
+                       void** mc_ptr);
+int b2_fd_listen(const char* name);
+int b2_fd_serve(int listen_sock, const int* fds, int nfds, int count);
+int b2_fd_fetch(const char* name, int which, int timeout_ms);
+void b2_fd_close(int fd);
+int b2_watchdog_start(int timeout_s, int device, int abort_on_fire);
+void b2_watchdog_watch(void* cuda_event);
+int b2_watchdog_fired(void);
+void b2_watchdog_stop(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Collectives over peer memory, fused with scale + SGD (csrc/allreduce.cu). Never call NCCL.
+ * Reference: resnet/main.py:80 (DDP bucket all-reduce, parameter/buffer broadcast), :124 (optimizer.step()).
+ * offset_bytes locates the bucket inside every rank's window (ctx->data[r]); n = fp32 element count (mult. of 4).
+ * p32 == NULL: reduce only. write_grad: leave the averaged gradient in this rank's bucket (p.grad parity).
+ * ---------------------------------------------------------------------------------------------- */
+enum { B2_AR_AUTO = 0, B2_AR_ONESHOT = 1, B2_AR_TWOSHOT = 2, B2_AR_MULTIMEM = 3 };
+long long b2_allreduce_oneshot_max_elems(int nblocks);
+int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long n, int algo, float scale,
+                 float* p32, float* mom, void* shadow_bf16, float lr, float momentum, float weight_decay,
+                 int first_step, int write_grad, int nblocks, void* stream);
+int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbytes, int src, void* dst_override,
+                 int nblocks, void* stream);
+int b2_xgpu_barrier(const b2_xgpu_ctx* ctx, int channel, void* stream);
 
 #ifdef __cplusplus
 }

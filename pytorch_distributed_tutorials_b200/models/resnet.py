@@ -1,0 +1,420 @@
+"""ResNet-18/34/50/101/152 with torchvision's parameter names, shapes and initialisation, executed by a
+hand-scheduled sm_100a engine instead of autograd-over-aten.
+
+The module tree is ordinary ``nn.Conv2d`` / ``nn.BatchNorm2d`` / ``nn.Linear`` containers, so ``state_dict()`` has
+exactly torchvision's keys (reference resnet/main.py:76 uses ``torchvision.models.resnet18``; checkpoints of the
+reference load here and vice versa, modulo the ``module.`` prefix the DDP wrapper adds, resnet/main.py:84,112).
+On CUDA the forward pass is ONE autograd node (``_EngineFn``): its forward runs conv (tcgen05 implicit GEMM) ->
+BN statistics -> BN-apply+ReLU(+residual) kernels and records a tape; its backward walks the tape with fused
+BN-backward(+ReLU mask, + gradient fan-in) -> dgrad / wgrad kernels, writes parameter gradients straight into
+their DDP bucket slots and tells the reducer as each one lands.  On CPU (gloo plumbing config) or with
+``B200DDP_FORCE_TORCH=1`` the same modules run through stock PyTorch ops, which is also the numerical oracle.
+"""
+from typing import List, Optional, Type, Union
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops import _lib, conv as convops, native
+from ..parallel.flat import store_of
+
+
+def conv3x3(inp, out, stride=1):
+    return nn.Conv2d(inp, out, 3, stride, 1, bias=False)
+
+
+def conv1x1(inp, out, stride=1):
+    return nn.Conv2d(inp, out, 1, stride, 0, bias=False)
+
+
+class BasicBlock(nn.Module):
+    expansion = 1
+
+    def __init__(self, inplanes, planes, stride=1, downsample=None, norm_layer=nn.BatchNorm2d):
+        super().__init__()
+        self.conv1 = conv3x3(inplanes, planes, stride)
+        self.bn1 = norm_layer(planes)
+        self.relu = nn.ReLU(inplace=True)
+        self.conv2 = conv3x3(planes, planes)
+        self.bn2 = norm_layer(planes)
+        self.downsample = downsample
+        self.stride = stride
+
+    def forward(self, x):
+        identity = x
+        out = self.relu(self.bn1(self.conv1(x)))
+        out = self.bn2(self.conv2(out))
+        if self.downsample is not None:
+            identity = self.downsample(x)
+        return self.relu(out + identity)
+
+    def units(self):
+        return [(self.conv1, self.bn1), (self.conv2, self.bn2)]
+
+
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, inplanes, planes, stride=1, downsample=None, norm_layer=nn.BatchNorm2d):
+        super().__init__()
+        self.conv1 = conv1x1(inplanes, planes)
+        self.bn1 = norm_layer(planes)
+        self.conv2 = conv3x3(planes, planes, stride)  # stride on the 3x3 ("v1.5"), as torchvision
+        self.bn2 = norm_layer(planes)
+        self.conv3 = conv1x1(planes, planes * self.expansion)
+        self.bn3 = norm_layer(planes * self.expansion)
+        self.relu = nn.ReLU(inplace=True)
+        self.downsample = downsample
+        self.stride = stride
+
+    def forward(self, x):
+        identity = x
+        out = self.relu(self.bn1(self.conv1(x)))
+        out = self.relu(self.bn2(self.conv2(out)))
+        out = self.bn3(self.conv3(out))
+        if self.downsample is not None:
+            identity = self.downsample(x)
+        return self.relu(out + identity)
+
+    def units(self):
+        return [(self.conv1, self.bn1), (self.conv2, self.bn2), (self.conv3, self.bn3)]
+
+
+class ResNet(nn.Module):
+    def __init__(self, block: Type[Union[BasicBlock, Bottleneck]], layers: List[int], num_classes: int = 1000,
+                 norm_layer=nn.BatchNorm2d):
+        super().__init__()
+        self._norm_layer = norm_layer
+        self.inplanes = 64
+        self.conv1 = nn.Conv2d(3, 64, 7, 2, 3, bias=False)
+        self.bn1 = norm_layer(64)
+        self.relu = nn.ReLU(inplace=True)
+        self.maxpool = nn.MaxPool2d(3, 2, 1)
+        self.layer1 = self._make_layer(block, 64, layers[0])
+        self.layer2 = self._make_layer(block, 128, layers[1], 2)
+        self.layer3 = self._make_layer(block, 256, layers[2], 2)
+        self.layer4 = self._make_layer(block, 512, layers[3], 2)
+        self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
+        self.fc = nn.Linear(512 * block.expansion, num_classes)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+            elif isinstance(m, (nn.BatchNorm2d, nn.GroupNorm)):
+                nn.init.constant_(m.weight, 1)
+                nn.init.constant_(m.bias, 0)
+        self._engine = None
+
+    def _make_layer(self, block, planes, blocks, stride=1):
+        downsample = None
+        if stride != 1 or self.inplanes != planes * block.expansion:
+            downsample = nn.Sequential(conv1x1(self.inplanes, planes * block.expansion, stride),
+                                       self._norm_layer(planes * block.expansion))
+        layers = [block(self.inplanes, planes, stride, downsample, self._norm_layer)]
+        self.inplanes = planes * block.expansion
+        for _ in range(1, blocks):
+            layers.append(block(self.inplanes, planes, norm_layer=self._norm_layer))
+        return nn.Sequential(*layers)
+
+    # ------------------------------------------------------------------ stock path (CPU / oracle)
+    def forward_reference(self, x):
+        x = self.maxpool(self.relu(self.bn1(self.conv1(x))))
+        x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        return self.fc(torch.flatten(self.avgpool(x), 1))
+
+    def forward(self, x):
+        if _lib.use_native(x) and next(self.parameters()).is_cuda:
+            if self._engine is None:
+                self._engine = ResNetEngine(self)
+                self._engine.xg = getattr(self, "_b2_xgpu_ctx", None)
+            return self._engine(x)
+        return self.forward_reference(x)
+
+    def grad_ready_order(self):
+        """Parameters in the order the engine's backward produces their gradients (last layer first)."""
+        order = [self.fc.bias, self.fc.weight]
+        for layer in (self.layer4, self.layer3, self.layer2, self.layer1):
+            for blk in reversed(list(layer)):
+                us = blk.units()
+                last_conv, last_bn = us[-1]
+                order += [last_bn.weight, last_bn.bias, last_conv.weight]
+                for c, b in reversed(us[:-1]):
+                    order += [b.weight, b.bias, c.weight]
+                if blk.downsample is not None:
+                    order += [blk.downsample[1].weight, blk.downsample[1].bias, blk.downsample[0].weight]
+        order += [self.bn1.weight, self.bn1.bias, self.conv1.weight]
+        return order
+
+
+def _resnet(block, layers, **kw):
+    return ResNet(block, layers, **kw)
+
+
+def resnet18(pretrained=False, **kw):
+    return _resnet(BasicBlock, [2, 2, 2, 2], **kw)
+
+
+def resnet34(pretrained=False, **kw):
+    return _resnet(BasicBlock, [3, 4, 6, 3], **kw)
+
+
+def resnet50(pretrained=False, **kw):
+    return _resnet(Bottleneck, [3, 4, 6, 3], **kw)
+
+
+def resnet101(pretrained=False, **kw):
+    return _resnet(Bottleneck, [3, 4, 23, 3], **kw)
+
+
+def resnet152(pretrained=False, **kw):
+    return _resnet(Bottleneck, [3, 8, 36, 3], **kw)
+
+
+MODELS = {"resnet18": resnet18, "resnet34": resnet34, "resnet50": resnet50, "resnet101": resnet101,
+          "resnet152": resnet152}
+
+
+# =====================================================================================================
+# Native engine
+# =====================================================================================================
+class _BnState:
+    """Persistent per-BatchNorm device buffers (saved statistics and kernel coefficient scratch)."""
+
+    def __init__(self, bn, device):
+        c = bn.num_features
+        self.mean = torch.empty(c, dtype=torch.float32, device=device)
+        self.invstd = torch.empty(c, dtype=torch.float32, device=device)
+        self.scale_shift = torch.empty(2 * c, dtype=torch.float32, device=device)
+        self.coef = torch.empty(3 * c, dtype=torch.float32, device=device)
+
+
+class _Rec:
+    __slots__ = ("x", "y", "z", "conv", "bn", "relu", "stem_a")
+
+    def __init__(self, x, y, z, conv, bn, relu, stem_a=None):
+        self.x, self.y, self.z, self.conv, self.bn, self.relu, self.stem_a = x, y, z, conv, bn, relu, stem_a
+
+
+class ResNetEngine:
+    """Runs a :class:`ResNet` on the native kernels. One instance per model; holds only scratch state."""
+
+    def __init__(self, model: ResNet):
+        self.model = model
+        self.device = next(model.parameters()).device
+        self.bn_state = {}
+        self.local_shadow = {}     # bf16 copies for parameters that are not in a FlatParameterStore
+        self.local_versions = {}
+        self.stem_wp = torch.zeros(64, 192, dtype=torch.bfloat16, device=self.device)
+        self.stem_dwp = torch.zeros(64, 192, dtype=torch.float32, device=self.device)
+        self.params = list(model.parameters())
+        self.xg = None             # XgpuCtx for SyncBatchNorm (set by parallel.syncbn)
+
+    # ------------------------------------------------------------------ helpers
+    def _bn(self, bn):
+        st = self.bn_state.get(id(bn))
+        if st is None:
+            st = _BnState(bn, self.device)
+            self.bn_state[id(bn)] = st
+        return st
+
+    def _w16(self, p):
+        st = store_of(p)
+        if st is not None and st.device.type == "cuda":
+            return st.shadow_view(p)
+        v = self.local_versions.get(id(p))
+        if v != p._version or id(p) not in self.local_shadow:
+            self.local_shadow[id(p)] = p.detach().to(torch.bfloat16).contiguous(
+                memory_format=torch.channels_last if p.dim() == 4 else torch.contiguous_format)
+            self.local_versions[id(p)] = p._version
+        return self.local_shadow[id(p)]
+
+    def _sync_shadows(self):
+        seen = set()
+        for p in self.params:
+            st = store_of(p)
+            if st is not None and id(st) not in seen:
+                seen.add(id(st))
+                st.sync_shadow()
+
+    def _sync_bn_ctx(self, bn):
+        return self.xg if getattr(bn, "_b2_sync", False) and self.xg is not None else None
+
+    # ------------------------------------------------------------------ forward units
+    def _conv(self, x, conv):
+        return convops.conv_fprop(x, self._w16(conv.weight), conv.stride[0], conv.padding[0])
+
+    def _unit(self, x, conv, bn, relu, res, training, tape):
+        y = self._conv(x, conv)
+        z = self._bn_apply(y, bn, relu, res, training)
+        if tape is not None:
+            tape.append(_Rec(x, y, z, conv, bn, relu))
+        return z
+
+    def _bn_apply(self, y, bn, relu, res, training):
+        st = self._bn(bn)
+        use_batch_stats = training or bn.running_mean is None
+        if use_batch_stats:
+            track = bn.track_running_stats and bn.running_mean is not None and training
+            mom = bn.momentum if bn.momentum is not None else 0.1
+            return native.bn_fwd_train(y, res, bn.weight, bn.bias, bn.running_mean if track else None,
+                                       bn.running_var if track else None,
+                                       bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
+                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn))
+        return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
+                                  st.scale_shift)
+
+    def _stem(self, x, training, tape):
+        m = self.model
+        xin = x if x.dtype in (torch.float32, torch.bfloat16) else x.float()
+        a, ho, wo = native.stem_im2col(xin.contiguous())
+        native.stem_pack_w(m.conv1.weight.detach(), self.stem_wp)  # fp32 OHWI [64,147] -> bf16 [64,192]
+        y2d = convops.gemm_nt(a, self.stem_wp)
+        n = x.shape[0]
+        y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
+        z = self._bn_apply(y, m.bn1, True, None, training)
+        if tape is not None:
+            tape.append(_Rec(None, y, z, m.conv1, m.bn1, True, stem_a=a))
+        return z
+
+    def _run_forward(self, x, training, tape):
+        m = self.model
+        self._sync_shadows()
+        z = self._stem(x, training, tape)
+        p = native.maxpool_fwd(z)
+        block_tapes = []
+        cur = p
+        for layer in (m.layer1, m.layer2, m.layer3, m.layer4):
+            for blk in layer:
+                bt = [] if tape is not None else None
+                us = blk.units()
+                h = cur
+                for conv, bn in us[:-1]:
+                    h = self._unit(h, conv, bn, True, None, training, bt)
+                if blk.downsample is not None:
+                    idn = self._unit(cur, blk.downsample[0], blk.downsample[1], False, None, training, bt)
+                else:
+                    idn = cur
+                conv, bn = us[-1]
+                cur = self._unit(h, conv, bn, True, idn, training, bt)
+                if tape is not None:
+                    block_tapes.append((blk, bt))
+        pooled = native.avgpool_fwd(cur)
+        logits = convops.gemm_nt(pooled, self._w16(m.fc.weight), m.fc.bias.detach())
+        if tape is not None:
+            tape.append(("head", z, p, block_tapes, cur.shape, pooled))
+        return logits
+
+    # ------------------------------------------------------------------ backward units
+    def _deliver(self, p, writer):
+        """Write p's gradient (writer(out, accumulate)) into its bucket slot, or return a fresh tensor."""
+        st = store_of(p)
+        if st is not None and p.requires_grad:
+            gv, acc = st.grad_slot(p)
+            writer(gv, acc)
+            st.publish_grad(p, gv)
+            return None
+        out = torch.empty(p.shape, dtype=torch.float32, device=self.device)
+        if p.dim() == 4:
+            out = out.contiguous(memory_format=torch.channels_last)
+        writer(out, False)
+        return out
+
+    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads):
+        conv, bn = rec.conv, rec.bn
+        st = self._bn(bn)
+        # BN backward needs dgamma/dbeta destinations up front (the finalize kernel writes them).
+        dg_slot = self._slot(bn.weight)
+        db_slot = self._slot(bn.bias)
+        dy, dres = native.bn_bwd(dz_a, dz_b, rec.z if rec.relu else None, rec.y, bn.weight, st.mean, st.invstd,
+                                 dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
+                                 self._sync_bn_ctx(bn))
+        self._publish(bn.weight, dg_slot, grads)
+        self._publish(bn.bias, db_slot, grads)
+        w = conv.weight
+        if rec.stem_a is not None:
+            dy2d = dy.permute(0, 2, 3, 1).reshape(-1, 64)
+            convops.gemm_tn(dy2d, rec.stem_a, self.stem_dwp)
+            g = self._deliver(w, lambda out, acc: native.stem_unpack_dw(self.stem_dwp, out, acc))
+            grads[id(w)] = g
+            return None, dres
+        s, pd = conv.stride[0], conv.padding[0]
+        g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
+        grads[id(w)] = g
+        dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd) if need_dx else None
+        return dx, dres
+
+    def _slot(self, p):
+        st = store_of(p)
+        if st is not None and p.requires_grad:
+            gv, acc = st.grad_slot(p)
+            return (gv, acc, st)
+        return (torch.empty(p.shape, dtype=torch.float32, device=self.device), False, None)
+
+    def _publish(self, p, slot, grads):
+        gv, _, st = slot
+        if st is not None:
+            st.publish_grad(p, gv)
+            grads[id(p)] = None
+        else:
+            grads[id(p)] = gv
+
+    def _run_backward(self, tape, dlogits):
+        m = self.model
+        grads = {}
+        head = tape[-1]
+        _, stem_z, pool_out, block_tapes, feat_shape, pooled = head
+        dl = dlogits if dlogits.dtype == torch.bfloat16 else dlogits.to(torch.bfloat16)
+        dl = dl.contiguous()
+        # classifier: bias grad (column sum), weight grad (dl^T @ pooled), input grad (dl @ W)
+        grads[id(m.fc.bias)] = self._deliver(m.fc.bias, lambda out, acc: native.colsum_bf16(dl, out, acc))
+        grads[id(m.fc.weight)] = self._deliver(m.fc.weight, lambda out, acc: convops.gemm_tn(dl, pooled, out, acc))
+        dpooled = convops.gemm_nn(dl, self._w16(m.fc.weight))
+        da, db = native.avgpool_bwd(dpooled, feat_shape), None
+        for blk, bt in reversed(block_tapes):
+            n_main = len(blk.units())
+            recs_main = bt[:n_main - 1]
+            rec_ds = bt[n_main - 1] if blk.downsample is not None else None
+            rec_last = bt[-1]
+            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads)
+            for rec in reversed(recs_main):
+                d, _ = self._unit_bwd(rec, d, None, True, False, grads)
+            if rec_ds is not None:
+                dds, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
+                da, db = d, dds
+            else:
+                da, db = d, dres
+        dz = native.maxpool_bwd(stem_z, da, db)
+        self._unit_bwd(tape[0], dz, None, False, False, grads)
+        return grads
+
+    # ------------------------------------------------------------------ entry
+    def __call__(self, x):
+        m = self.model
+        training = m.training
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.params):
+            return _EngineFn.apply(self, x, training, *self.params)
+        return self._run_forward(x, training, None).float()
+
+
+class _EngineFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, engine, x, training, *params):
+        tape = []
+        logits = engine._run_forward(x, training, tape)
+        ctx.engine = engine
+        ctx.tape = tape
+        ctx.nparams = len(params)
+        return logits.float()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        engine = ctx.engine
+        tape, ctx.tape = ctx.tape, None
+        if tape is None:
+            raise RuntimeError("the native engine's activations were already consumed by a previous backward()")
+        grads = engine._run_backward(tape, dlogits)
+        out = []
+        for p in engine.params:
+            g = grads.get(id(p))
+            out.append(g if (g is not None and p.requires_grad) else None)
+        return (None, None, None) + tuple(out)

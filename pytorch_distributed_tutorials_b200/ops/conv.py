@@ -33,16 +33,53 @@ def _is_cl(t):
 
 
 def native_ok(x, w):
-    return (_lib.use_native(x) and x.dtype == torch.bfloat16 and x.shape[1] % 64 == 0 and w.shape[0] % 64 == 0)
+    return (_lib.use_native(x) and x.dtype == torch.bfloat16 and x.shape[1] % 64 == 0 and w.shape[0] % 8 == 0)
 
 
-def conv_fprop(x, w, stride, pad):
-    """x: [N,Cin,H,W] bf16 channels_last; w: [Cout,Cin,KH,KW] bf16 channels_last -> y bf16 channels_last."""
+def gemm_nt(a, w, bias=None):
+    """a [M,K] bf16 @ w[N,K]^T (+bias) -> [M,N] bf16 on the fprop kernel (1x1 conv view). K % 64 == 0, N % 8 == 0."""
+    M, K = a.shape
+    N = w.shape[0]
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    e = _lib.lib().b2_conv_fprop(_lib.ptr(a), _lib.ptr(w), _lib.ptr(bias), _lib.ptr(y), M, 1, 1, K, N, 1, 1, 1, 0,
+                                 _lib.stream_ptr())
+    _lib.check(e, "b2_conv_fprop(gemm_nt)")
+    _lib.count_launch()
+    return y
+
+
+def gemm_nn(dy, w):
+    """dy [M,N] bf16 @ w[N,K] -> [M,K] bf16 on the dgrad kernel. K % 64 == 0, N % 8 == 0."""
+    M, N = dy.shape
+    K = w.shape[1]
+    dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
+    e = _lib.lib().b2_conv_dgrad(_lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), M, 1, 1, K, N, 1, 1, 1, 0,
+                                 _lib.stream_ptr())
+    _lib.check(e, "b2_conv_dgrad(gemm_nn)")
+    _lib.count_launch()
+    return dx
+
+
+def gemm_tn(dy, a, out, accumulate=False):
+    """out[N,K] fp32 (+)= dy[M,N]^T @ a[M,K] on the wgrad kernel (split-K over M). K % 64 == 0, N % 8 == 0."""
+    M, N = dy.shape
+    K = a.shape[1]
+    ws = workspace(a.device)
+    e = _lib.lib().b2_conv_wgrad(_lib.ptr(a), _lib.ptr(dy), _lib.ptr(out), _lib.ptr(ws), _lib.c_ll(ws.numel() * 4),
+                                 M, 1, 1, K, N, 1, 1, 1, 0, int(accumulate), _lib.stream_ptr())
+    _lib.check(e, "b2_conv_wgrad(gemm_tn)")
+    _lib.count_launch(2)
+    return out
+
+
+def conv_fprop(x, w, stride, pad, bias=None):
+    """x: [N,Cin,H,W] bf16 channels_last; w: [Cout,Cin,KH,KW] bf16 channels_last -> y bf16 channels_last.
+    ``bias`` (fp32 [Cout], optional) is added in the epilogue (classifier)."""
     N, H, W, Cin, Cout, KH, KW, s, p = _geom(x, w, stride, pad)
     Ho, Wo = (H + 2 * p - KH) // s + 1, (W + 2 * p - KW) // s + 1
     assert _is_cl(x) and _is_cl(w), "conv_fprop expects channels_last operands"
     y = torch.empty((N, Cout, Ho, Wo), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
-    e = _lib.lib().b2_conv_fprop(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), N, H, W, Cin, Cout, KH, KW, s, p,
+    e = _lib.lib().b2_conv_fprop(_lib.ptr(x), _lib.ptr(w), _lib.ptr(bias), _lib.ptr(y), N, H, W, Cin, Cout, KH, KW, s, p,
                                  _lib.stream_ptr())
     _lib.check(e, "b2_conv_fprop")
     _lib.count_launch()

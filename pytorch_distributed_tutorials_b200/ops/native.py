@@ -1,0 +1,200 @@
+"""Thin tensor-level wrappers over the C ABI (include/b200ddp.h) for everything except convolution
+(see ops/conv.py).  All tensors are CUDA; activations are bf16 ``channels_last`` (NHWC in memory).
+
+Each wrapper names the aten op(s) of the reference's dependency stack it stands in for; the reference
+itself only reaches them through torchvision / nn / optim one-liners (reference resnet/main.py:76,102,103).
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import c_ll, c_f, c_p, ptr, stream_ptr, check, count_launch
+
+_scratch = {}
+
+
+def scratch(device, key, numel, dtype=torch.float32):
+    """Persistent per-device scratch buffers (no per-step allocation; CUDA-graph friendly)."""
+    k = (device, key)
+    t = _scratch.get(k)
+    if t is None or t.numel() < numel or t.dtype != dtype:
+        t = torch.empty(numel, dtype=dtype, device=device)
+        _scratch[k] = t
+    return t
+
+
+def bn_partial(device):
+    return scratch(device, "bn_partial", 1184 * 2 * 2048)
+
+
+class XgpuCtx(ctypes.Structure):
+    """Mirror of ``b2_xgpu_ctx``."""
+    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("data", ctypes.c_void_p * 8),
+                ("flags", ctypes.c_void_p * 8), ("epoch", ctypes.c_void_p)]
+
+
+def _xg(xg):
+    return ctypes.byref(xg) if xg is not None else None
+
+
+def _mc(t):
+    """[N,C,H,W] channels_last -> (M, C)."""
+    n, c, h, w = t.shape
+    return n * h * w, c
+
+
+# ------------------------------------------------------------------------------------------------ batch norm
+def bn_fwd_train(y, res, gamma, beta, running_mean, running_var, nbt, momentum, eps, relu, mean, invstd,
+                 scale_shift, xg=None, xg_slot=0):
+    """aten::native_batch_norm (training) + relu_ + add_ fused. Returns z."""
+    M, C = _mc(y)
+    z = torch.empty_like(y)
+    e = _lib.lib().b2_bn_fwd_train(ptr(y), ptr(res), ptr(z), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
+                                   ptr(running_var), ptr(nbt), c_f(momentum), c_f(eps), int(relu), ptr(mean),
+                                   ptr(invstd), ptr(scale_shift), ptr(bn_partial(y.device)), _xg(xg), xg_slot,
+                                   stream_ptr())
+    check(e, "b2_bn_fwd_train")
+    count_launch(3)
+    return z
+
+
+def bn_fwd_eval(y, res, gamma, beta, running_mean, running_var, eps, relu, scale_shift):
+    M, C = _mc(y)
+    z = torch.empty_like(y)
+    e = _lib.lib().b2_bn_fwd_eval(ptr(y), ptr(res), ptr(z), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
+                                  ptr(running_var), c_f(eps), int(relu), ptr(scale_shift), stream_ptr())
+    check(e, "b2_bn_fwd_eval")
+    count_launch(2)
+    return z
+
+
+def bn_bwd(dz_a, dz_b, z, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, want_dres, xg=None,
+           xg_slot=0):
+    """aten::native_batch_norm_backward + threshold_backward + the gradient fan-in add, fused.
+    Returns (dy, dres) where dres (optional) is the masked incoming gradient for the residual branch."""
+    M, C = _mc(y)
+    dy = torch.empty_like(y)
+    dres = torch.empty_like(y) if want_dres else None
+    e = _lib.lib().b2_bn_bwd(ptr(dz_a), ptr(dz_b), ptr(z), ptr(y), ptr(dy), ptr(dres), c_ll(M), C, ptr(gamma),
+                             ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta), int(accumulate), int(relu), ptr(coef),
+                             ptr(bn_partial(y.device)), _xg(xg), xg_slot, stream_ptr())
+    check(e, "b2_bn_bwd")
+    count_launch(3)
+    return dy, dres
+
+
+# ------------------------------------------------------------------------------------------------ pooling
+def maxpool_fwd(x):
+    """aten::max_pool2d_with_indices 3x3/2/1 (indices are recomputed in backward instead of stored)."""
+    n, c, h, w = x.shape
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    check(_lib.lib().b2_maxpool_fwd(ptr(x), ptr(y), n, h, w, c, stream_ptr()), "b2_maxpool_fwd")
+    count_launch()
+    return y
+
+
+def maxpool_bwd(x, dy_a, dy_b=None):
+    n, c, h, w = x.shape
+    dx = torch.empty_like(x)
+    check(_lib.lib().b2_maxpool_bwd(ptr(x), ptr(dy_a), ptr(dy_b), ptr(dx), n, h, w, c, stream_ptr()),
+          "b2_maxpool_bwd")
+    count_launch()
+    return dx
+
+
+def avgpool_fwd(x):
+    """aten::mean.dim over H,W -> [N, C] bf16."""
+    n, c, h, w = x.shape
+    y = torch.empty((n, c), dtype=x.dtype, device=x.device)
+    check(_lib.lib().b2_avgpool_fwd(ptr(x), ptr(y), n, h * w, c, stream_ptr()), "b2_avgpool_fwd")
+    count_launch()
+    return y
+
+
+def avgpool_bwd(dy, shape):
+    n, c, h, w = shape
+    dx = torch.empty(shape, dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
+    check(_lib.lib().b2_avgpool_bwd(ptr(dy), ptr(dx), n, h * w, c, stream_ptr()), "b2_avgpool_bwd")
+    count_launch()
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------ loss
+def ce_fwd(logits, labels):
+    """aten::_log_softmax + nll_loss_forward (mean). logits bf16 [rows, ncls]. Returns (loss fp32 scalar, lse)."""
+    rows, ncls = logits.shape
+    lse = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    loss_row = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    check(_lib.lib().b2_ce_fwd(ptr(logits), ptr(labels), ptr(lse), ptr(loss_row), ptr(loss), rows, ncls,
+                               logits.stride(0), stream_ptr()), "b2_ce_fwd")
+    count_launch(2)
+    return loss, lse
+
+
+def ce_bwd(logits, labels, lse, gscale, dbias=None, accumulate_bias=False):
+    rows, ncls = logits.shape
+    dlogits = torch.empty_like(logits)
+    check(_lib.lib().b2_ce_bwd(ptr(logits), ptr(labels), ptr(lse), ptr(gscale), ptr(dlogits), ptr(dbias),
+                               int(accumulate_bias), rows, ncls, logits.stride(0), stream_ptr()), "b2_ce_bwd")
+    count_launch(2 if dbias is not None else 1)
+    return dlogits
+
+
+def colsum_bf16(m, out, accumulate=False):
+    rows, cols = m.shape
+    check(_lib.lib().b2_colsum_bf16(ptr(m), ptr(out), rows, cols, m.stride(0), int(accumulate), stream_ptr()),
+          "b2_colsum_bf16")
+    count_launch()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ optimizer
+def sgd_step(p, g, buf, shadow, lr, momentum, weight_decay, grad_scale, first_step):
+    """torch.optim.SGD (momentum, weight decay, dampening 0) on flat fp32 buffers + bf16 shadow refresh."""
+    n = p.numel()
+    check(_lib.lib().b2_sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), c_ll(n), c_f(lr), c_f(momentum),
+                                 c_f(weight_decay), c_f(grad_scale), int(first_step), stream_ptr()), "b2_sgd_step")
+    count_launch()
+
+
+def cast_f32_bf16(src, dst):
+    check(_lib.lib().b2_cast_f32_bf16(ptr(src), ptr(dst), c_ll(src.numel()), stream_ptr()), "b2_cast_f32_bf16")
+    count_launch()
+
+
+# ------------------------------------------------------------------------------------------------ stem / layout
+def stem_im2col(x):
+    """[N,3,H,W] fp32/bf16 NCHW -> im2col matrix [N*Ho*Wo, 192] bf16 for the 7x7/2 stem (K padded 147 -> 192)."""
+    n, c, h, w = x.shape
+    assert c == 3 and x.is_contiguous()
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    a = torch.empty((n * ho * wo, 192), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().b2_stem_im2col(ptr(x), int(x.dtype == torch.bfloat16), ptr(a), n, h, w, stream_ptr()),
+          "b2_stem_im2col")
+    count_launch()
+    return a, ho, wo
+
+
+def stem_pack_w(w_fp32, out):
+    check(_lib.lib().b2_stem_pack_w(ptr(w_fp32), ptr(out), w_fp32.shape[0], stream_ptr()), "b2_stem_pack_w")
+    count_launch()
+    return out
+
+
+def stem_unpack_dw(dwp, dw, accumulate):
+    check(_lib.lib().b2_stem_unpack_dw(ptr(dwp), ptr(dw), dw.shape[0], int(accumulate), stream_ptr()),
+          "b2_stem_unpack_dw")
+    count_launch()
+
+
+def nchw_to_nhwc_bf16(x):
+    n, c, h, w = x.shape
+    assert x.is_contiguous()
+    y = torch.empty((n, c, h, w), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    check(_lib.lib().b2_nchw_to_nhwc_bf16(ptr(x), int(x.dtype == torch.bfloat16), ptr(y), n, c, h * w,
+                                          stream_ptr()), "b2_nchw_to_nhwc_bf16")
+    count_launch()
+    return y

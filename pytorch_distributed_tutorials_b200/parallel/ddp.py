@@ -1,0 +1,297 @@
+"""DistributedDataParallel-style wrapper with a native reducer and pluggable collectives.
+
+Same surface as ``torch.nn.parallel.DistributedDataParallel`` as the reference uses it (reference
+resnet/main.py:80 ``DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)``, then
+``.parameters()``, ``.state_dict()`` / ``.load_state_dict()`` with ``module.``-prefixed keys at :84,:112,
+``.train()`` / ``.eval()`` at :24,:117 and ``__call__`` at :31,:121), plus ``no_sync()``.
+
+What happens underneath is different:
+  * construction: parameter shapes are verified across ranks, parameters are moved into flat per-bucket buffers
+    (gradient buckets in symmetric memory on CUDA), parameters and buffers are broadcast from rank 0;
+  * buckets are planned once, in the order gradients become ready (known statically for our ResNets, reverse
+    registration order otherwise), 1 MiB first bucket / 25 MiB cap by default like torch;
+  * during ``loss.backward()`` each gradient lands directly in its bucket slot; the native reducer
+    (csrc/reducer.cpp) launches, strictly in bucket order, one fused all-reduce(+SGD) kernel per full bucket on a
+    high-priority stream, overlapped with the rest of backward;
+  * a no-grad / eval forward issues **zero** collectives (the reference's rank-0-only evaluation at
+    resnet/main.py:110-111 therefore cannot desynchronise the ranks).
+"""
+import contextlib
+import ctypes
+import os
+import weakref
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..ops import _lib
+from .comm import LocalComm, P2PComm, TorchComm
+from .flat import FlatParameterStore, plan_buckets
+
+MiB = 1 << 20
+
+
+def _ready_order(module, params):
+    if hasattr(module, "grad_ready_order"):
+        order = [p for p in module.grad_ready_order() if p.requires_grad]
+        ids = {id(p) for p in order}
+        if len(order) == len(params) and ids == {id(p) for p in params}:
+            return order
+    return list(reversed(params))
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
+                 process_group=None, bucket_cap_mb=None, find_unused_parameters=False,
+                 gradient_as_bucket_view=True, static_graph=False, backend=None, comm_algo=None,
+                 init_sync=True):
+        super().__init__()
+        if find_unused_parameters:
+            raise NotImplementedError("find_unused_parameters is not supported (ResNets use every parameter)")
+        self.module = module
+        self.process_group = process_group
+        self.broadcast_buffers = broadcast_buffers
+        self.require_backward_grad_sync = True
+        self.gradient_as_bucket_view = True
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            raise RuntimeError("DistributedDataParallel needs at least one parameter that requires grad")
+        self.device = params[0].device
+        if device_ids is not None and len(device_ids) == 1 and self.device.type == "cuda":
+            want = torch.device("cuda", device_ids[0]) if isinstance(device_ids[0], int) else torch.device(
+                device_ids[0])
+            if want.index is not None and want != self.device:
+                raise ValueError("module is on %s but device_ids=%s" % (self.device, device_ids))
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
+
+        # ---- bucket plan (gradient-ready order; torch's 1 MiB first bucket only with the default cap)
+        ordered = _ready_order(module, params)
+        if bucket_cap_mb is None:
+            first_cap, cap = 1 * MiB, 25 * MiB
+        else:
+            first_cap, cap = -1, int(bucket_cap_mb * MiB)
+        sizes = [p.numel() * p.element_size() for p in ordered]
+        self.bucket_of_param = plan_buckets(sizes, first_cap, cap)
+        self.bucket_cap_bytes = cap
+
+        # ---- K1: every rank must hold the same parameter shapes
+        if self.world > 1:
+            sig = [tuple(p.shape) for p in ordered]
+            sigs = [None] * self.world
+            dist.all_gather_object(sigs, sig, group=process_group)
+            for r, s in enumerate(sigs):
+                if s != sig:
+                    raise RuntimeError("parameter shapes differ between rank %d and rank %d" % (self.rank, r))
+
+        # ---- collective back end
+        backend = backend or os.environ.get("B200DDP_BACKEND")
+        if backend is None:
+            if self.world == 1:
+                backend = "local"
+            elif self.device.type == "cuda" and _lib.use_native():
+                backend = "p2p"
+            else:
+                backend = "torch"
+        buffers = [b for b in module.buffers()]
+        if backend == "p2p":
+            total = sum((p.numel() + 63) // 64 * 64 for p in ordered) * 4
+            buf_bytes = sum((b.numel() * b.element_size() + 255) // 256 * 256 for b in buffers)
+            extra = 16 * MiB + 2 * buf_bytes + 2 * MiB  # staging, buffer region, SyncBN slots
+            self.comm = P2PComm(self.device, process_group, total + extra, algo=comm_algo)
+        elif backend == "local":
+            self.comm = LocalComm(process_group)
+        elif backend == "torch":
+            self.comm = TorchComm(process_group)
+        else:
+            raise ValueError("unknown backend %r" % backend)
+        self.backend = backend
+
+        # ---- flat storage; gradients are bucket views from now on
+        self.store = FlatParameterStore(ordered, self.bucket_of_param, self.device,
+                                        grad_alloc=self.comm.grad_alloc if backend == "p2p" else None)
+        self.store.on_ready = self._on_param_ready
+        self._param_index = {id(p): i for i, p in enumerate(ordered)}
+        self.ordered_params = ordered
+
+        # ---- module buffers (BN running stats): one flat region; symmetric on the P2P backend so that the
+        #      per-iteration sync (K3) is a single in-place pull from rank 0
+        self._buffers_flat = None
+        self._setup_buffers(buffers)
+
+        # ---- K2: initial parameter + buffer broadcast from rank 0
+        if init_sync and self.world > 1:
+            self._sync_module_states()
+
+        L = _lib.lib()
+        arr = (ctypes.c_int * len(ordered))(*self.bucket_of_param)
+        L.b2_reducer_create.restype = ctypes.c_void_p
+        self._reducer = ctypes.c_void_p(L.b2_reducer_create(len(ordered), arr, len(self.store.buckets)))
+        self._launch_buf = (ctypes.c_int * max(1, len(self.store.buckets)))()
+        self._finalizer = weakref.finalize(self, L.b2_reducer_destroy, self._reducer)
+        self._callback_queued = False
+        self._fused_args = None
+        self._in_backward_iteration = False
+        self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook) for p in ordered]
+        self.iterations = 0
+        self.xgpu_compute_ctx = self.comm.window.ctx(P2PComm.PAD_COMPUTE) if backend == "p2p" else None
+        self._install_syncbn_ctx()
+        self._watchdog_evt = None
+        wd = int(os.environ.get("B200DDP_WATCHDOG_SEC", "0"))
+        if wd > 0 and self.device.type == "cuda":
+            L.b2_watchdog_start(wd, self.device.index or 0, 1)
+            self._watchdog = True
+        else:
+            self._watchdog = False
+
+    # ------------------------------------------------------------------ buffers
+    def _setup_buffers(self, buffers):
+        self._buffer_list = buffers
+        if not buffers or self.backend != "p2p":
+            return
+        total = sum((b.numel() * b.element_size() + 255) // 256 * 256 for b in buffers)
+        region = self.comm.alloc_tensor(total, torch.uint8)
+        off = 0
+        owners = {}
+        for name, mod in self.module.named_modules():
+            for bname, b in mod._buffers.items():
+                if b is not None:
+                    owners[id(b)] = (mod, bname)
+        with torch.no_grad():
+            for b in buffers:
+                nb = b.numel() * b.element_size()
+                v = region[off:off + nb].view(b.dtype).view(b.shape)
+                v.copy_(b)
+                mod, bname = owners[id(b)]
+                mod._buffers[bname] = v
+                off += (nb + 255) // 256 * 256
+        self._buffers_flat = region
+        self._buffer_list = [b for b in self.module.buffers()]
+
+    def _sync_buffers(self):
+        """K3: broadcast BN buffers from rank 0 before a training forward."""
+        if self.world == 1 or not self._buffer_list:
+            return
+        if self._buffers_flat is not None:
+            self.comm.launch_log.append(("broadcast", len(self._buffer_list)))
+            self.comm.broadcast_window_(self.comm.window.offset_of(self._buffers_flat), self._buffers_flat.numel(), 0)
+        else:
+            with torch.no_grad():
+                self.comm.broadcast_(self._buffer_list, 0)
+
+    def _sync_module_states(self):
+        with torch.no_grad():
+            if self.backend == "p2p":
+                # stage parameters through the (symmetric) gradient buckets: copy, pull from rank 0, copy back
+                self.comm.launch_log.append(("broadcast", len(self.ordered_params) + len(self._buffer_list)))
+                for b in self.store.buckets:
+                    if self.rank == 0:
+                        b.g32.copy_(b.p32)
+                    self.comm.broadcast_window_(self.comm.window.offset_of(b.g32), b.numel * 4, 0)
+                    if self.rank != 0:
+                        b.p32.copy_(b.g32)
+                    b.g32.zero_()
+                if self._buffers_flat is not None:
+                    self.comm.broadcast_window_(self.comm.window.offset_of(self._buffers_flat),
+                                                self._buffers_flat.numel(), 0)
+                self.comm.barrier()
+                torch.cuda.synchronize(self.device)
+            else:
+                self.comm.broadcast_([b.p32 for b in self.store.buckets] + list(self._buffer_list), 0)
+        self.store.shadow_fresh = False
+
+    def _install_syncbn_ctx(self):
+        eng = getattr(self.module, "_engine", None)
+        self._syncbn_ctx = self.xgpu_compute_ctx
+        if hasattr(self.module, "_engine"):
+            # the engine is created lazily; hand it the context through the model
+            self.module._b2_xgpu_ctx = self.xgpu_compute_ctx
+            if eng is not None:
+                eng.xg = self.xgpu_compute_ctx
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, *inputs, **kwargs):
+        grad_mode = torch.is_grad_enabled()
+        if grad_mode and self.module.training:
+            if self.require_backward_grad_sync:
+                _lib.lib().b2_reducer_reset(self._reducer)
+                self._callback_queued = False
+                self._fused_args = None
+                self._in_backward_iteration = True
+                self.comm.begin_backward()
+            if self.broadcast_buffers:
+                self._sync_buffers()
+        return self.module(*inputs, **kwargs)
+
+    # ------------------------------------------------------------------ reducer hooks
+    def _autograd_hook(self, p):
+        """Generic path: autograd accumulated p.grad. Make it a bucket view (once), then mark ready."""
+        gv = self.store.grad_view(p)
+        if p.grad is not None and p.grad.data_ptr() != gv.data_ptr():
+            gv.copy_(p.grad)
+            p.grad = gv
+        self._on_param_ready(p)
+
+    def _on_param_ready(self, p):
+        if not self.require_backward_grad_sync or not self._in_backward_iteration:
+            return
+        idx = self._param_index.get(id(p))
+        if idx is None:
+            return
+        if not self._callback_queued:
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+        n = _lib.lib().b2_reducer_mark_ready(self._reducer, idx, self._launch_buf)
+        if n == -1:
+            raise RuntimeError("a parameter was marked ready twice in one iteration (second backward() through "
+                               "the same forward? use no_sync() for gradient accumulation)")
+        for i in range(n):
+            self._launch_bucket(self.store.buckets[self._launch_buf[i]])
+
+    def _launch_bucket(self, bucket):
+        opt = self.store.optimizer
+        sgd = None
+        if opt is not None and opt.fuse_with_backward and self.backend in ("p2p", "local") and opt._native_ok():
+            if self._fused_args is None:
+                self._fused_args = opt.prepare_fused(self.store)
+            sgd = self._fused_args
+        if self.world == 1 and sgd is None:
+            self.comm.launch_log.append(("allreduce", bucket.index))
+            return
+        self.comm.allreduce_bucket(bucket, sgd=sgd)
+        if sgd is not None:
+            opt.note_bucket_updated(bucket)
+
+    def _finalize_backward(self):
+        self._callback_queued = False
+        self._in_backward_iteration = False
+        left = _lib.lib().b2_reducer_unlaunched(self._reducer)
+        self.comm.finalize()
+        if self._fused_args is not None:
+            self.store.mark_params_updated_natively()
+        if self._watchdog:
+            self._watchdog_evt = torch.cuda.Event()
+            self._watchdog_evt.record()
+            _lib.lib().b2_watchdog_watch(ctypes.c_void_p(self._watchdog_evt.cuda_event))
+        self.iterations += 1
+        if left:
+            raise RuntimeError("%d gradient bucket(s) never became ready: some parameters took no part in the "
+                               "loss (find_unused_parameters is not supported)" % left)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Accumulate gradients locally; the next backward outside the context reduces the sum."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    # ------------------------------------------------------------------ introspection
+    def bucket_sizes(self):
+        return [b.used for b in self.store.buckets]
+
+    def collective_log(self):
+        return list(self.comm.launch_log)
