@@ -13,7 +13,7 @@
 namespace b2 {
 
 constexpr int kBnThreads = 256;
-constexpr int kMaxPartialBlocks = 1184;  // 148 SMs x 8
+constexpr int kMaxPartialBlocks = 592;  // 148 SMs x 4
 
 struct Vec8 {
   float v[8];
@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
   const long long row0 = blockIdx.x * rows_per_blk;
   const long long row1 = min(M, row0 + rows_per_blk);
   if (r < RP) {
+#pragma unroll 4
     for (long long row = row0 + r; row < row1; row += RP) {
       Vec8 v = load_bf16x8(y + row * C + cv * 8);
 #pragma unroll
@@ -83,41 +84,68 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
 
 // Finalize: partial sums -> mean / invstd / running stats / fused scale+shift.  With world > 1 the per-GPU
 // totals (sum, sumsq, count) are exchanged through symmetric memory inside this kernel (SyncBatchNorm).
-__global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
-                                   const float* __restrict__ gamma, const float* __restrict__ beta,
-                                   float* running_mean, float* running_var, long long* num_batches_tracked,
-                                   float momentum, float eps, float* mean_out, float* invstd_out, float* scale_out,
-                                   float* shift_out, XgpuCtx xg, int slot_off) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  float s = 0.f, ss = 0.f;
-  if (c < C) {
-    for (int b = 0; b < nblk; ++b) {
-      s += partial[(size_t)b * 2 * C + c];
-      ss += partial[(size_t)b * 2 * C + C + c];
-    }
+// One CTA per 8 channels: 32 row-groups x 8 channels read the partials sector-coalesced, then a fixed-order
+// shared-memory reduction (deterministic).
+constexpr int kFinCh = 8;
+constexpr int kFinGroups = 32;
+constexpr int kFinThreads = kFinCh * kFinGroups;
+
+B2_DEVICE void fin_reduce2(const float* __restrict__ partial, int nblk, int C, int c, int rg, int cg, float* sm,
+                           float& out0, float& out1) {
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll 4
+  for (int b = rg; b < nblk; b += kFinGroups) {
+    a0 += partial[(size_t)b * 2 * C + c];
+    a1 += partial[(size_t)b * 2 * C + C + c];
   }
+  sm[rg * kFinCh + cg] = a0;
+  sm[kFinThreads + rg * kFinCh + cg] = a1;
+  __syncthreads();
+  if (rg == 0) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int g = 0; g < kFinGroups; ++g) {
+      s0 += sm[g * kFinCh + cg];
+      s1 += sm[kFinThreads + g * kFinCh + cg];
+    }
+    out0 = s0;
+    out1 = s1;
+  }
+}
+
+__global__ void __launch_bounds__(kFinThreads)
+    bn_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
+                       const float* __restrict__ gamma, const float* __restrict__ beta, float* running_mean,
+                       float* running_var, long long* num_batches_tracked, float momentum, float eps,
+                       float* mean_out, float* invstd_out, float* scale_out, float* shift_out, XgpuCtx xg,
+                       int slot_off) {
+  __shared__ float sm[2 * kFinThreads];
+  const int cg = threadIdx.x % kFinCh, rg = threadIdx.x / kFinCh;
+  const int c = blockIdx.x * kFinCh + cg;
+  float s = 0.f, ss = 0.f;
+  fin_reduce2(partial, nblk, C, c, rg, cg, sm, s, ss);
   float total = count;
   if (xg.world > 1) {
     // Publish this GPU's totals, then read everybody's in rank order (identical result on every rank).
     float* mine = xg.data[xg.rank] + slot_off;
-    if (c < C) {
+    if (rg == 0) {
       mine[c] = s;
       mine[C + c] = ss;
     }
     if (threadIdx.x == 0) mine[2 * C + blockIdx.x] = count;
     xgpu_barrier(xg, /*channel=*/blockIdx.x);
     s = 0.f; ss = 0.f; total = 0.f;
-    for (int rk = 0; rk < xg.world; ++rk) {
-      const float* peer = xg.data[rk] + slot_off;
-      if (c < C) {
+    if (rg == 0) {
+      for (int rk = 0; rk < xg.world; ++rk) {
+        const float* peer = xg.data[rk] + slot_off;
         s += ld_relaxed_sys_f32(peer + c);
         ss += ld_relaxed_sys_f32(peer + C + c);
+        total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
       }
-      total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
     }
     xgpu_barrier(xg, blockIdx.x);  // nobody overwrites its slot while a peer may still be reading it
   }
-  if (c >= C) return;
+  if (rg != 0) return;
   const float mean = s / total;
   float var = ss / total - mean * mean;
   var = fmaxf(var, 0.f);
@@ -191,6 +219,7 @@ __global__ void __launch_bounds__(kBnThreads)
   const long long row1 = min(M, row0 + rows_per_blk);
   if (r < RP) {
     Vec8 mu = load_f32x8(mean + cv * 8);
+#pragma unroll 2
     for (long long row = row0 + r; row < row1; row += RP) {
       const long long off = row * C + cv * 8;
       Vec8 g = load_bf16x8(dza + off);
@@ -219,41 +248,39 @@ __global__ void __launch_bounds__(kBnThreads)
 
 // partials -> dgamma/dbeta (fp32, optionally accumulated into existing grads) and the three per-channel
 // coefficients of  dy = k1*dz' + k2*y + k3.  With world > 1 the two sums are reduced across GPUs in-kernel.
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
-                                       const float* __restrict__ gamma, const float* __restrict__ mean,
-                                       const float* __restrict__ invstd, float* dgamma, float* dbeta, int accumulate,
-                                       float* coef, XgpuCtx xg, int slot_off) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kFinThreads)
+    bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float count,
+                           const float* __restrict__ gamma, const float* __restrict__ mean,
+                           const float* __restrict__ invstd, float* dgamma, float* dbeta, int accumulate,
+                           float* coef, XgpuCtx xg, int slot_off) {
+  __shared__ float sm[2 * kFinThreads];
+  const int cg = threadIdx.x % kFinCh, rg = threadIdx.x / kFinCh;
+  const int c = blockIdx.x * kFinCh + cg;
   float sdy = 0.f, sdx = 0.f;
-  if (c < C) {
-    for (int b = 0; b < nblk; ++b) {
-      sdy += partial[(size_t)b * 2 * C + c];
-      sdx += partial[(size_t)b * 2 * C + C + c];
-    }
-  }
+  fin_reduce2(partial, nblk, C, c, rg, cg, sm, sdy, sdx);
   // Local sums give this rank's dgamma/dbeta (DDP averages them later, as torch's SyncBatchNorm does).
   const float sdy_local = sdy, sdx_local = sdx;
   float total = count;
   if (xg.world > 1) {
     float* mine = xg.data[xg.rank] + slot_off;
-    if (c < C) {
+    if (rg == 0) {
       mine[c] = sdy;
       mine[C + c] = sdx;
     }
     if (threadIdx.x == 0) mine[2 * C + blockIdx.x] = count;
     xgpu_barrier(xg, blockIdx.x);
     sdy = 0.f; sdx = 0.f; total = 0.f;
-    for (int rk = 0; rk < xg.world; ++rk) {
-      const float* peer = xg.data[rk] + slot_off;
-      if (c < C) {
+    if (rg == 0) {
+      for (int rk = 0; rk < xg.world; ++rk) {
+        const float* peer = xg.data[rk] + slot_off;
         sdy += ld_relaxed_sys_f32(peer + c);
         sdx += ld_relaxed_sys_f32(peer + C + c);
+        total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
       }
-      total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
     }
     xgpu_barrier(xg, blockIdx.x);
   }
-  if (c >= C) return;
+  if (rg != 0) return;
   const float is = invstd[c], mu = mean[c], g = gamma[c];
   const float dg = sdx_local * is, db = sdy_local;
   if (dgamma) dgamma[c] = accumulate ? dgamma[c] + dg : dg;
@@ -335,8 +362,7 @@ extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, long lon
   const int RP = kBnThreads / (C / 8);
   bn_stats_kernel<<<nblk, kBnThreads, 2 * RP * C * sizeof(float), st>>>((const __nv_bfloat16*)y, partial, M, C, rpb);
   XgpuCtx ctx = xgpu_from_c(xg);
-  const int fthreads = 128;
-  bn_finalize_kernel<<<(C + fthreads - 1) / fthreads, fthreads, 0, st>>>(
+  bn_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(
       partial, nblk, C, (float)M, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, mean,
       invstd, scale_shift, scale_shift + C, ctx, xg_slot);
   const long long nvec = M * (C / 8);
@@ -396,7 +422,7 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
   B2_BWD_DISPATCH(RED, 0);
 #undef RED
   XgpuCtx ctx = xgpu_from_c(xg);
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, nblk, C, (float)M, gamma, mean, invstd, dgamma,
+  bn_bwd_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(partial, nblk, C, (float)M, gamma, mean, invstd, dgamma,
                                                           dbeta, accumulate, coef, ctx, xg_slot);
   const long long nvec = M * (C / 8);
   const int grid = stream_grid(nvec);

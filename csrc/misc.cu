@@ -23,9 +23,12 @@ B2_DEVICE uint4 pack8(const float (&v)[8]) {
 }
 
 // ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
+// Forward also records which of the 9 taps won (first maximum in (kh,kw) scan order, the tie rule of
+// aten::max_pool2d_with_indices) as one byte per output element, so backward is a pure gather.
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
-                                                          __nv_bfloat16* __restrict__ y, int N, int H, int W, int C8,
-                                                          int Ho, int Wo) {
+                                                          __nv_bfloat16* __restrict__ y,
+                                                          unsigned char* __restrict__ idx, int N, int H, int W,
+                                                          int C8, int Ho, int Wo) {
   const long long total = (long long)N * Ho * Wo * C8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -35,8 +38,9 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
     const int oh = (int)(pix % Ho);
     const int n = (int)(pix / Ho);
     float m[8];
+    unsigned arg[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
       const int h = oh * 2 - 1 + kh;
@@ -48,17 +52,24 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
         float v[8];
         unpack8(*reinterpret_cast<const uint4*>(x + (((long long)(n * H + h) * W + w) * C8 + cv) * 8), v);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], v[j]);
+        for (int j = 0; j < 8; ++j)
+          if (v[j] > m[j] || arg[j] == 255u) { m[j] = v[j]; arg[j] = kh * 3 + kw; }
       }
     }
     *reinterpret_cast<uint4*>(y + i * 8) = pack8(m);
+    if (idx) {
+      uint2 o;
+      o.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+      o.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+      *reinterpret_cast<uint2*>(idx + i * 8) = o;
+    }
   }
 }
 
-// dx[h,w] = sum over the (<=4) windows containing (h,w) of (dy_a [+ dy_b])[window] * [argmax(window) == (h,w)].
+// dx[h,w] = sum over the (<=4) windows containing (h,w) of (dy_a [+ dy_b])[window] * [winner(window) == (h,w)].
 template <bool TWO>
 __global__ void __launch_bounds__(256)
-    maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dya,
+    maxpool_bwd_kernel(const unsigned char* __restrict__ idx, const __nv_bfloat16* __restrict__ dya,
                        const __nv_bfloat16* __restrict__ dyb, __nv_bfloat16* __restrict__ dx, int N, int H, int W,
                        int C8, int Ho, int Wo) {
   const long long total = (long long)N * H * W * C8;
@@ -76,26 +87,9 @@ __global__ void __launch_bounds__(256)
     const int ow0 = w >> 1, ow1 = min(Wo - 1, (w + 1) >> 1);
     for (int oh = oh0; oh <= oh1; ++oh) {
       for (int ow = ow0; ow <= ow1; ++ow) {
-        float best[8];
-        int arg[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = -1; }
-#pragma unroll
-        for (int kh = 0; kh < 3; ++kh) {
-          const int hh = oh * 2 - 1 + kh;
-          if (hh < 0 || hh >= H) continue;
-#pragma unroll
-          for (int kw = 0; kw < 3; ++kw) {
-            const int ww = ow * 2 - 1 + kw;
-            if (ww < 0 || ww >= W) continue;
-            float v[8];
-            unpack8(*reinterpret_cast<const uint4*>(x + (((long long)(n * H + hh) * W + ww) * C8 + cv) * 8), v);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (v[j] > best[j] || arg[j] < 0) { best[j] = v[j]; arg[j] = hh * W + ww; }
-          }
-        }
+        const unsigned code = (unsigned)((h - (oh * 2 - 1)) * 3 + (w - (ow * 2 - 1)));
         const long long o = (((long long)(n * Ho + oh) * Wo + ow) * C8 + cv) * 8;
+        const uint2 id = *reinterpret_cast<const uint2*>(idx + o);
         float g[8];
         unpack8(*reinterpret_cast<const uint4*>(dya + o), g);
         if (TWO) {
@@ -104,9 +98,11 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] += g2[j];
         }
-        const int self = h * W + w;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += (arg[j] == self) ? g[j] : 0.f;
+        for (int j = 0; j < 4; ++j) {
+          acc[j] += (((id.x >> (8 * j)) & 0xFFu) == code) ? g[j] : 0.f;
+          acc[4 + j] += (((id.y >> (8 * j)) & 0xFFu) == code) ? g[4 + j] : 0.f;
+        }
       }
     }
     *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
@@ -324,24 +320,24 @@ static int sgrid(long long n, int per = 256) {
 using namespace b2;
 typedef __nv_bfloat16 bf16;
 
-extern "C" int b2_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
+extern "C" int b2_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream) {
   if (C % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   maxpool_fwd_kernel<<<sgrid((long long)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, (bf16*)y, N, H, W, C / 8, Ho, Wo);
+      (const bf16*)x, (bf16*)y, (unsigned char*)idx, N, H, W, C / 8, Ho, Wo);
   return cudaGetLastError();
 }
-extern "C" int b2_maxpool_bwd(const void* x, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
-                              void* stream) {
+extern "C" int b2_maxpool_bwd(const void* idx, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W,
+                              int C, void* stream) {
   if (C % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const int grid = sgrid((long long)N * H * W * (C / 8));
   if (dy_b)
-    maxpool_bwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (const bf16*)dy_a,
+    maxpool_bwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const unsigned char*)idx, (const bf16*)dy_a,
                                                                       (const bf16*)dy_b, (bf16*)dx, N, H, W, C / 8, Ho, Wo);
   else
-    maxpool_bwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (const bf16*)dy_a, nullptr,
-                                                                       (bf16*)dx, N, H, W, C / 8, Ho, Wo);
+    maxpool_bwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const unsigned char*)idx, (const bf16*)dy_a,
+                                                                       nullptr, (bf16*)dx, N, H, W, C / 8, Ho, Wo);
   return cudaGetLastError();
 }
 extern "C" int b2_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {

@@ -16,7 +16,7 @@ extern "C" {
 #endif
 
 #define B2_MAX_WORLD 8
-#define B2_XGPU_CHANNELS 64
+#define B2_XGPU_CHANNELS 256
 
 /* Peer-memory context handed to kernels that talk to other GPUs (built by b2_symm_* below).
  * data[r]/flags[r] are this process's mappings of rank r's symmetric window and signal pad;
@@ -74,8 +74,9 @@ int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, 
  * Reference: resnet/main.py:76 (maxpool / avgpool / fc of torchvision resnet), :102 (CrossEntropyLoss),
  * :103 and :124 (optim.SGD momentum 0.9, weight_decay 1e-5, step()).
  * ---------------------------------------------------------------------------------------------- */
-int b2_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);            /* 3x3 / 2 / pad 1 */
-int b2_maxpool_bwd(const void* x, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
+/* 3x3 / stride 2 / pad 1. idx (optional, u8 [N,Ho,Wo,C]) records the winning tap for the backward pass. */
+int b2_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
+int b2_maxpool_bwd(const void* idx, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
                    void* stream);
 int b2_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
 int b2_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);

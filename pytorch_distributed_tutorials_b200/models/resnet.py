@@ -267,7 +267,10 @@ class ResNetEngine:
         m = self.model
         xin = x if x.dtype in (torch.float32, torch.bfloat16) else x.float()
         a, ho, wo = native.stem_im2col(xin.contiguous())
-        native.stem_pack_w(m.conv1.weight.detach(), self.stem_wp)  # fp32 OHWI [64,147] -> bf16 [64,192]
+        w_ohwi = m.conv1.weight.detach().permute(0, 2, 3, 1)   # a free view when the weight is stored OHWI
+        if not w_ohwi.is_contiguous():
+            w_ohwi = w_ohwi.contiguous()
+        native.stem_pack_w(w_ohwi, self.stem_wp)                # fp32 OHWI [64,147] -> bf16 [64,192]
         y2d = convops.gemm_nt(a, self.stem_wp)
         n = x.shape[0]
         y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
@@ -280,7 +283,7 @@ class ResNetEngine:
         m = self.model
         self._sync_shadows()
         z = self._stem(x, training, tape)
-        p = native.maxpool_fwd(z)
+        p, pool_idx = native.maxpool_fwd(z, with_index=tape is not None)
         block_tapes = []
         cur = p
         for layer in (m.layer1, m.layer2, m.layer3, m.layer4):
@@ -301,7 +304,7 @@ class ResNetEngine:
         pooled = native.avgpool_fwd(cur)
         logits = convops.gemm_nt(pooled, self._w16(m.fc.weight), m.fc.bias.detach())
         if tape is not None:
-            tape.append(("head", z, p, block_tapes, cur.shape, pooled))
+            tape.append(("head", z.shape, pool_idx, block_tapes, cur.shape, pooled))
         return logits
 
     # ------------------------------------------------------------------ backward units
@@ -362,7 +365,7 @@ class ResNetEngine:
         m = self.model
         grads = {}
         head = tape[-1]
-        _, stem_z, pool_out, block_tapes, feat_shape, pooled = head
+        _, stem_shape, pool_idx, block_tapes, feat_shape, pooled = head
         dl = dlogits if dlogits.dtype == torch.bfloat16 else dlogits.to(torch.bfloat16)
         dl = dl.contiguous()
         # classifier: bias grad (column sum), weight grad (dl^T @ pooled), input grad (dl @ W)
@@ -383,7 +386,7 @@ class ResNetEngine:
                 da, db = d, dds
             else:
                 da, db = d, dres
-        dz = native.maxpool_bwd(stem_z, da, db)
+        dz = native.maxpool_bwd(pool_idx, stem_shape, da, db)
         self._unit_bwd(tape[0], dz, None, False, False, grads)
         return grads
 

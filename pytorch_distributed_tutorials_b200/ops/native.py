@@ -25,7 +25,7 @@ def scratch(device, key, numel, dtype=torch.float32):
 
 
 def bn_partial(device):
-    return scratch(device, "bn_partial", 1184 * 2 * 2048)
+    return scratch(device, "bn_partial", 592 * 2 * 2048)
 
 
 class XgpuCtx(ctypes.Structure):
@@ -85,20 +85,21 @@ def bn_bwd(dz_a, dz_b, z, y, gamma, mean, invstd, dgamma, dbeta, accumulate, rel
 
 
 # ------------------------------------------------------------------------------------------------ pooling
-def maxpool_fwd(x):
-    """aten::max_pool2d_with_indices 3x3/2/1 (indices are recomputed in backward instead of stored)."""
+def maxpool_fwd(x, with_index=True):
+    """aten::max_pool2d_with_indices 3x3/2/1. Returns (y, idx) where idx holds the winning tap (u8) per element."""
     n, c, h, w = x.shape
     ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
     y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
-    check(_lib.lib().b2_maxpool_fwd(ptr(x), ptr(y), n, h, w, c, stream_ptr()), "b2_maxpool_fwd")
+    idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device) if with_index else None
+    check(_lib.lib().b2_maxpool_fwd(ptr(x), ptr(y), ptr(idx), n, h, w, c, stream_ptr()), "b2_maxpool_fwd")
     count_launch()
-    return y
+    return y, idx
 
 
-def maxpool_bwd(x, dy_a, dy_b=None):
-    n, c, h, w = x.shape
-    dx = torch.empty_like(x)
-    check(_lib.lib().b2_maxpool_bwd(ptr(x), ptr(dy_a), ptr(dy_b), ptr(dx), n, h, w, c, stream_ptr()),
+def maxpool_bwd(idx, x_shape, dy_a, dy_b=None):
+    n, c, h, w = x_shape
+    dx = torch.empty(x_shape, dtype=dy_a.dtype, device=dy_a.device, memory_format=torch.channels_last)
+    check(_lib.lib().b2_maxpool_bwd(ptr(idx), ptr(dy_a), ptr(dy_b), ptr(dx), n, h, w, c, stream_ptr()),
           "b2_maxpool_bwd")
     count_launch()
     return dx

@@ -186,7 +186,7 @@ class P2PComm(_Base):
     def barrier(self, stream=None, pad=None):
         st = stream or torch.cuda.current_stream(self.device)
         pad = self.PAD_COMPUTE if pad is None else pad
-        check(_lib.lib().b2_xgpu_barrier(ctypes.byref(self.window.ctx(pad)), 63, c_p(st.cuda_stream)),
+        check(_lib.lib().b2_xgpu_barrier(ctypes.byref(self.window.ctx(pad)), 255, c_p(st.cuda_stream)),
               "b2_xgpu_barrier")
 
     def finalize(self):

@@ -133,6 +133,9 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._fused_args = None
         self._in_backward_iteration = False
+        self._ready_ids = set()
+        self.measure_exposed = os.environ.get("B200DDP_MEASURE_EXPOSED", "1") == "1"
+        self._exposed_events = []
         self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook) for p in ordered]
         self.iterations = 0
         self.xgpu_compute_ctx = self.comm.window.ctx(P2PComm.PAD_COMPUTE) if backend == "p2p" else None
@@ -219,6 +222,7 @@ class DistributedDataParallel(nn.Module):
                 self._callback_queued = False
                 self._fused_args = None
                 self._in_backward_iteration = True
+                self._ready_ids = set()
                 self.comm.begin_backward()
             if self.broadcast_buffers:
                 self._sync_buffers()
@@ -231,14 +235,17 @@ class DistributedDataParallel(nn.Module):
         if p.grad is not None and p.grad.data_ptr() != gv.data_ptr():
             gv.copy_(p.grad)
             p.grad = gv
-        self._on_param_ready(p)
+        self._on_param_ready(p, from_autograd=True)
 
-    def _on_param_ready(self, p):
+    def _on_param_ready(self, p, from_autograd=False):
         if not self.require_backward_grad_sync or not self._in_backward_iteration:
             return
         idx = self._param_index.get(id(p))
         if idx is None:
             return
+        if from_autograd and id(p) in self._ready_ids:
+            return  # the native engine already delivered this gradient; autograd's hook still fires afterwards
+        self._ready_ids.add(id(p))
         if not self._callback_queued:
             self._callback_queued = True
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
@@ -267,6 +274,14 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._in_backward_iteration = False
         left = _lib.lib().b2_reducer_unlaunched(self._reducer)
+        if self.measure_exposed and self.backend == "p2p":
+            # exposed communication = how long the reductions outlast backward's own kernels
+            ev_c, ev_m = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev_c.record(torch.cuda.current_stream(self.device))
+            ev_m.record(self.comm.stream)
+            self._exposed_events.append((ev_c, ev_m))
+            if len(self._exposed_events) > 512:
+                self._exposed_events = self._exposed_events[-256:]
         self.comm.finalize()
         if self._fused_args is not None:
             self.store.mark_params_updated_natively()
@@ -288,6 +303,15 @@ class DistributedDataParallel(nn.Module):
             yield
         finally:
             self.require_backward_grad_sync = old
+
+    def exposed_comm_ms(self, last=None):
+        """Mean time per step by which the gradient reductions outlasted backward compute (device events)."""
+        if not self._exposed_events:
+            return 0.0 if self.world == 1 else None
+        torch.cuda.synchronize(self.device)
+        evs = self._exposed_events[-last:] if last else self._exposed_events
+        vals = [max(0.0, c.elapsed_time(m)) for c, m in evs]
+        return sum(vals) / len(vals)
 
     # ------------------------------------------------------------------ introspection
     def bucket_sizes(self):

@@ -14,7 +14,8 @@ import torch.distributed as dist
 from ..ops import _lib
 from ..ops.native import XgpuCtx
 
-PAD_BYTES = 64 * 8 * 4     # one signal pad: 64 channels x 8 ranks x u32
+CHANNELS = 256            # B2_XGPU_CHANNELS
+PAD_BYTES = CHANNELS * 8 * 4   # one signal pad: 256 channels x 8 ranks x u32
 N_PADS = 8
 HEADER_BYTES = 64 << 10    # pads live at the start of every window
 MAX_WORLD = 8
@@ -70,7 +71,7 @@ class SymmetricWindow:
             self.transport = "ipc"
         else:
             self.transport = "vmm"
-        self.epochs = torch.zeros(N_PADS * 64, dtype=torch.int32, device=self.device)
+        self.epochs = torch.zeros(N_PADS * CHANNELS, dtype=torch.int32, device=self.device)
         self._ctx_cache = {}
         dist.barrier(group=group)
 
@@ -187,6 +188,6 @@ class SymmetricWindow:
             for r in range(self.world):
                 c.data[r] = self.ptrs[r]
                 c.flags[r] = self.ptrs[r] + pad * PAD_BYTES
-            c.epoch = self.epochs.data_ptr() + pad * 64 * 4
+            c.epoch = self.epochs.data_ptr() + pad * CHANNELS * 4
             self._ctx_cache[pad] = c
         return c

@@ -1,0 +1,112 @@
+"""End-to-end checks of the native ResNet engine on one B200 against the stock-PyTorch oracle path."""
+import copy
+import os
+
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _cos(a, b):
+    return torch.nn.functional.cosine_similarity(a.float().flatten(), b.float().flatten(), dim=0).item()
+
+
+@pytest.mark.parametrize("name,size,bs", [("resnet18", 64, 16), ("resnet50", 128, 8), ("resnet18", 32, 32)])
+def test_forward_backward_matches_oracle(name, size, bs):
+    """The engine (bf16 activations, fp32 statistics) against an fp32 run of the stock-op path with the same
+    weights. bf16 noise is calibrated with a third run: the stock path under bf16 autocast. The engine must be
+    about as close to fp32 as autocast is."""
+    from pytorch_distributed_tutorials_b200.models.resnet import MODELS
+    torch.manual_seed(0)
+    m = MODELS[name]().to(DEV)
+    ref32 = copy.deepcopy(m)
+    ref16 = copy.deepcopy(m)
+    x = torch.randn(bs, 3, size, size, device=DEV)
+    y = torch.randint(0, 1000, (bs,), device=DEV)
+    out = m(x)
+    assert out.shape == (bs, 1000) and out.dtype == torch.float32
+    loss = nn.functional.cross_entropy(out, y)
+    loss.backward()
+    out32 = ref32.forward_reference(x)
+    loss32 = nn.functional.cross_entropy(out32, y)
+    loss32.backward()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out16 = ref16.forward_reference(x)
+    nn.functional.cross_entropy(out16.float(), y).backward()
+    assert abs(loss.item() - loss32.item()) < 0.03 * abs(loss32.item())
+    assert _cos(out, out32) > min(0.99, _cos(out16, out32) - 0.02), (_cos(out, out32), _cos(out16, out32))
+    bad = []
+    for (n, p), (_, q32), (_, q16) in zip(m.named_parameters(), ref32.named_parameters(),
+                                           ref16.named_parameters()):
+        assert p.grad is not None, n
+        c, c16 = _cos(p.grad, q32.grad), _cos(q16.grad, q32.grad)
+        if c < min(0.98, c16 - 0.04):  # as close to fp32 as the stock bf16 path is
+            bad.append((n, round(c, 4), round(c16, 4)))
+    assert not bad, bad
+    for (n, b), (_, c) in zip(m.named_buffers(), ref32.named_buffers()):
+        if n.endswith("num_batches_tracked"):
+            assert int(b) == int(c) == 1
+        else:
+            assert torch.allclose(b, c, atol=2e-2, rtol=5e-2), n
+
+
+def test_eval_mode_and_no_grad():
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    torch.manual_seed(1)
+    m = resnet18().to(DEV)
+    x = torch.randn(4, 3, 32, 32, device=DEV)
+    m.train()
+    m(x)  # populate running stats
+    m.eval()
+    with torch.no_grad():
+        a = m(x)
+        b = m.forward_reference(x)
+    assert _cos(a, b) > 0.995
+
+
+def test_training_loop_with_wrapper_and_fused_sgd_single_gpu():
+    """world_size 1: wrapper + flat store + our SGD (fused into the reducer epilogue) trains and tracks the oracle."""
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    torch.manual_seed(2)
+    base = resnet18().to(DEV)
+    ref = copy.deepcopy(base)
+    ddp = DistributedDataParallel(base, device_ids=[0])
+    opt = optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
+    opt_r = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5)
+    crit = CrossEntropyLoss()
+    x = torch.randn(32, 3, 32, 32, device=DEV)
+    y = torch.randint(0, 10, (32,), device=DEV)
+    ours, theirs = [], []
+    for _ in range(6):
+        opt.zero_grad()
+        l = crit(ddp(x), y)
+        l.backward()
+        opt.step()
+        ours.append(l.item())
+        opt_r.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            o = ref.forward_reference(x)
+        lr_ = nn.functional.cross_entropy(o.float(), y)
+        lr_.backward()
+        opt_r.step()
+        theirs.append(lr_.item())
+    assert ours[-1] < ours[0] * 0.8, ours          # it learns
+    assert abs(ours[0] - theirs[0]) < 0.05 * theirs[0]
+    assert abs(ours[-1] - theirs[-1]) < 0.35 * max(theirs[-1], 0.5), (ours, theirs)
+    sd = opt.state_dict()
+    assert len(sd["state"]) == 62 and "momentum_buffer" in sd["state"][0]
+    keys = list(ddp.state_dict().keys())
+    assert keys[0] == "module.conv1.weight" and len(keys) == 122
+
+
+def test_native_library_is_loaded():
+    from pytorch_distributed_tutorials_b200.ops import _lib
+    assert _lib.available()
+    maps = open("/proc/self/maps").read()
+    assert "libb200ddp.so" in maps

@@ -1,0 +1,200 @@
+"""Per-kernel numerics on a B200: every native op against a plain PyTorch fp32 reference of the same op
+(bf16 tolerances where the kernel's inputs/outputs are bf16)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _cl(t):
+    return t.contiguous(memory_format=torch.channels_last)
+
+
+def _bf(t):
+    return _cl(t.to(torch.bfloat16))
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6)).item()
+
+
+CONV_SHAPES = [  # ci, co, k, s, p, H, N
+    (64, 64, 1, 1, 0, 56, 4), (64, 64, 3, 1, 1, 56, 4), (256, 128, 1, 1, 0, 56, 2), (128, 128, 3, 2, 1, 56, 2),
+    (256, 512, 1, 2, 0, 56, 2), (512, 2048, 1, 1, 0, 7, 8), (512, 512, 3, 1, 1, 7, 8), (1024, 256, 1, 1, 0, 14, 4),
+    (64, 128, 3, 2, 1, 8, 8), (512, 512, 3, 1, 1, 1, 8), (256, 512, 1, 2, 0, 2, 8), (128, 256, 3, 2, 1, 28, 3),
+]
+
+
+@pytest.mark.parametrize("ci,co,k,s,p,H,N", CONV_SHAPES)
+def test_conv_fprop_dgrad_wgrad(ci, co, k, s, p, H, N):
+    from pytorch_distributed_tutorials_b200.ops import conv
+    torch.manual_seed(0)
+    x = _bf(torch.randn(N, ci, H, H, device=DEV))
+    w = _bf(torch.randn(co, ci, k, k, device=DEV) / (ci * k * k) ** 0.5)
+    Ho = (H + 2 * p - k) // s + 1
+    dy = _bf(torch.randn(N, co, Ho, Ho, device=DEV))
+    xf, wf, dyf = x.float(), w.float(), dy.float()
+    y = conv.conv_fprop(x, w, s, p)
+    assert y.shape == (N, co, Ho, Ho) and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, conv.ref_fprop(xf, wf, s, p)) < 1e-2
+    dx = conv.conv_dgrad(dy, w, x.shape, s, p)
+    assert _rel(dx, conv.ref_dgrad(dyf, wf, x.shape, s, p)) < 1e-2
+    dw = conv.conv_wgrad(x, dy, w.shape, s, p)
+    ref_dw = conv.ref_wgrad(xf, dyf, w.shape, s, p)
+    assert _rel(dw, ref_dw) < 2e-3
+    # accumulate into an existing gradient
+    dw2 = conv.conv_wgrad(x, dy, w.shape, s, p, out=dw.clone(), accumulate=True)
+    assert _rel(dw2, 2 * ref_dw) < 2e-3
+
+
+def test_gemm_helpers_classifier_shapes():
+    from pytorch_distributed_tutorials_b200.ops import conv
+    torch.manual_seed(1)
+    a = torch.randn(37, 2048, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(1000, 2048, device=DEV) / 45).to(torch.bfloat16)
+    b = torch.randn(1000, device=DEV)
+    y = conv.gemm_nt(a, w, b)
+    assert _rel(y, a.float() @ w.float().t() + b) < 1e-2
+    dy = torch.randn(37, 1000, device=DEV).to(torch.bfloat16)
+    assert _rel(conv.gemm_nn(dy, w), dy.float() @ w.float()) < 1e-2
+    out = torch.zeros(1000, 2048, device=DEV)
+    conv.gemm_tn(dy, a, out)
+    assert _rel(out, dy.float().t() @ a.float()) < 2e-3
+
+
+@pytest.mark.parametrize("C,H,N", [(64, 16, 4), (256, 14, 3), (2048, 7, 2), (128, 5, 1)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
+def test_bn_forward_backward(C, H, N, relu, res):
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(2)
+    y = _bf(torch.randn(N, C, H, H, device=DEV) * 2 + 0.5)
+    r = _bf(torch.randn(N, C, H, H, device=DEV)) if res else None
+    gamma = torch.rand(C, device=DEV) + 0.5
+    beta = torch.randn(C, device=DEV)
+    rm, rv = torch.randn(C, device=DEV), torch.rand(C, device=DEV) + 0.5
+    nbt = torch.tensor(3, device=DEV)
+    rm0, rv0 = rm.clone(), rv.clone()
+    mean, invstd = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+    ss, coef = torch.empty(2 * C, device=DEV), torch.empty(3 * C, device=DEV)
+    z = native.bn_fwd_train(y, r, gamma, beta, rm, rv, nbt, 0.1, 1e-5, relu, mean, invstd, ss)
+    # reference (fp32 math on the same bf16 inputs)
+    yf = y.float().requires_grad_(True)
+    g32, b32 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rf = r.float().requires_grad_(True) if res else None
+    rm_r, rv_r = rm0.clone(), rv0.clone()
+    o = F.batch_norm(yf, rm_r, rv_r, g32, b32, True, 0.1, 1e-5)
+    if res:
+        o = o + rf
+    if relu:
+        o = F.relu(o)
+    assert _rel(z, o) < 1e-2
+    assert torch.allclose(rm, rm_r, atol=1e-4, rtol=1e-4) and torch.allclose(rv, rv_r, atol=1e-4, rtol=1e-3)
+    assert int(nbt.item()) == 4
+    # backward with a two-way gradient fan-in
+    dza, dzb = _bf(torch.randn_like(o)), _bf(torch.randn_like(o))
+    dgamma, dbeta = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+    dy, dres = native.bn_bwd(dza, dzb, z if relu else None, y, gamma, mean, invstd, dgamma, dbeta, False, relu, coef,
+                             True)
+    # reference gradient must use the same relu mask as the kernel (bf16 z): build it from z
+    up = dza.float() + dzb.float()
+    if relu:
+        up = up * (z.float() > 0)
+    ob = F.batch_norm(yf, None, None, g32, b32, True, 0.1, 1e-5)
+    ob.backward(up)
+    assert _rel(dy, yf.grad) < 2e-2
+    assert _rel(dgamma, g32.grad) < 1e-2 and _rel(dbeta, b32.grad) < 1e-2
+    assert _rel(dres, up) < 1e-2
+
+
+def test_bn_eval():
+    from pytorch_distributed_tutorials_b200.ops import native
+    C = 128
+    y = _bf(torch.randn(2, C, 9, 9, device=DEV))
+    gamma, beta = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV)
+    rm, rv = torch.randn(C, device=DEV), torch.rand(C, device=DEV) + 0.5
+    z = native.bn_fwd_eval(y, None, gamma, beta, rm, rv, 1e-5, True, torch.empty(2 * C, device=DEV))
+    assert _rel(z, F.relu(F.batch_norm(y.float(), rm, rv, gamma, beta, False, 0.1, 1e-5))) < 1e-2
+
+
+@pytest.mark.parametrize("H", [112, 16, 7])
+def test_maxpool(H):
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(3)
+    x = _bf(F.relu(torch.randn(3, 64, H, H, device=DEV)))  # relu -> many ties at 0, like the real stem
+    y, idx = native.maxpool_fwd(x)
+    xf = x.float().requires_grad_(True)
+    yr = F.max_pool2d(xf, 3, 2, 1)
+    assert torch.equal(y.float(), yr)
+    da, db = _bf(torch.randn_like(yr)), _bf(torch.randn_like(yr))
+    dx = native.maxpool_bwd(idx, x.shape, da, db)
+    yr.backward(da.float() + db.float())
+    assert _rel(dx, xf.grad) < 1e-2
+
+
+def test_avgpool():
+    from pytorch_distributed_tutorials_b200.ops import native
+    x = _bf(torch.randn(5, 2048, 7, 7, device=DEV))
+    y = native.avgpool_fwd(x)
+    assert _rel(y, x.float().mean((2, 3))) < 1e-2
+    dy = torch.randn(5, 2048, device=DEV).to(torch.bfloat16)
+    dx = native.avgpool_bwd(dy, x.shape)
+    assert _rel(dx, (dy.float() / 49)[:, :, None, None].expand(5, 2048, 7, 7)) < 1e-2
+
+
+def test_cross_entropy():
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    torch.manual_seed(4)
+    logits = (torch.randn(33, 1000, device=DEV) * 3).to(torch.bfloat16).float().requires_grad_(True)
+    labels = torch.randint(0, 1000, (33,), device=DEV)
+    l = CrossEntropyLoss()(logits, labels)
+    (l * 2.0).backward()
+    ref = logits.detach().clone().requires_grad_(True)
+    lr = F.cross_entropy(ref, labels)
+    (lr * 2.0).backward()
+    assert abs(l.item() - lr.item()) < 1e-3
+    assert _rel(logits.grad, ref.grad) < 1e-2
+
+
+def test_sgd_matches_torch():
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(5)
+    n = 100003
+    p = torch.randn(n, device=DEV)
+    pr = p.clone().requires_grad_(True)
+    buf = torch.zeros(n, device=DEV)
+    sh = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    opt = torch.optim.SGD([pr], lr=0.01, momentum=0.9, weight_decay=1e-5)
+    for it in range(3):
+        g = torch.randn(n, device=DEV)
+        native.sgd_step(p, g, buf, sh, 0.01, 0.9, 1e-5, 1.0, it == 0)
+        pr.grad = g.clone()
+        opt.step()
+        assert torch.allclose(p, pr.detach(), atol=1e-6, rtol=1e-5)
+        assert torch.allclose(buf, opt.state[pr]["momentum_buffer"], atol=1e-6, rtol=1e-5)
+        assert torch.equal(sh, p.to(torch.bfloat16))
+
+
+def test_stem_conv_via_im2col():
+    from pytorch_distributed_tutorials_b200.ops import conv, native
+    torch.manual_seed(6)
+    x = torch.randn(3, 3, 64, 64, device=DEV)
+    w = torch.randn(64, 3, 7, 7, device=DEV) * 0.1
+    w_ohwi = w.permute(0, 2, 3, 1).contiguous()
+    wp = torch.zeros(64, 192, device=DEV, dtype=torch.bfloat16)
+    native.stem_pack_w(w_ohwi, wp)
+    a, ho, wo = native.stem_im2col(x)
+    y = conv.gemm_nt(a, wp).view(3, ho, wo, 64).permute(0, 3, 1, 2)
+    ref = F.conv2d(x.to(torch.bfloat16).float(), w.to(torch.bfloat16).float(), None, 2, 3)
+    assert _rel(y, ref) < 1e-2
+    # weight gradient: dW = dy^T @ A, unpacked to OHWI
+    dy = torch.randn(3 * ho * wo, 64, device=DEV).to(torch.bfloat16)
+    dwp = torch.zeros(64, 192, device=DEV)
+    conv.gemm_tn(dy, a, dwp)
+    dw = torch.zeros(64, 7, 7, 3, device=DEV)
+    native.stem_unpack_dw(dwp, dw, False)
+    ref_dw = conv.ref_wgrad(x.to(torch.bfloat16).float(), dy.float().view(3, ho, wo, 64).permute(0, 3, 1, 2),
+                            w.shape, 2, 3)
+    assert _rel(dw.permute(0, 3, 1, 2), ref_dw) < 5e-3

@@ -1,0 +1,212 @@
+"""Multi-GPU checks (>= 2 B200s on one node): P2P all-reduce / broadcast kernels against torch.distributed (NCCL),
+the fused reduce+SGD epilogue against unfused torch ops, the DDP wrapper against torch DDP, and SyncBatchNorm with
+in-kernel cross-GPU statistics against torch.nn.SyncBatchNorm."""
+import pytest
+import torch
+
+from _dist_utils import run_ranks
+
+pytestmark = pytest.mark.gpu
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+
+
+def _collectives(rank, world):
+    import torch.distributed as dist
+    from pytorch_distributed_tutorials_b200.parallel.comm import P2PComm
+    from pytorch_distributed_tutorials_b200.parallel.flat import Bucket
+    dev = torch.device("cuda", rank)
+    comm = P2PComm(dev, None, 600 << 20)
+    res = {"transport": comm.window.transport, "multicast": bool(comm.mc_base)}
+    sizes = [128, 4096, 129 * 1024, 513000 + 24, 7213056, 25 * 1024 * 1024 // 4]
+    algos = ["oneshot", "twoshot"] + (["multimem"] if comm.mc_base else [])
+
+    class FakeBucket:
+        pass
+
+    for n in sizes:
+        n = (n + 63) // 64 * 64
+        b = FakeBucket()
+        b.index, b.numel = 0, n
+        b.g32 = comm.grad_alloc(n)
+        for algo in algos:
+            if algo == "oneshot" and n > 524288:
+                continue
+            g = torch.Generator(device=dev).manual_seed(1000 * rank + n % 977)
+            local = torch.randn(n, device=dev, generator=g)
+            b.g32.copy_(local)
+            ref = local.clone()
+            dist.all_reduce(ref)
+            ref /= world
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_bucket(b, sgd=None, algo=algo)
+            comm.finalize()
+            torch.cuda.synchronize()
+            err = (b.g32 - ref).abs().max().item()
+            res["%s_%d" % (algo, n)] = err
+            # every rank must hold bit-identical results
+            mine = b.g32.clone()
+            other = mine.clone()
+            dist.broadcast(other, 0)
+            res["%s_%d_ident" % (algo, n)] = bool(torch.equal(mine, other))
+            dist.barrier()
+        # fused SGD epilogue vs unfused torch math (two steps: first-step buffer init, then momentum)
+        p = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(7))
+        b.p32, b.mom = p.clone(), torch.zeros(n, device=dev)
+        b.shadow = torch.empty(n, device=dev, dtype=torch.bfloat16)
+        pr, mr = p.clone(), None
+        for step in range(2):
+            g = torch.Generator(device=dev).manual_seed(31 * rank + step)
+            local = torch.randn(n, device=dev, generator=g)
+            b.g32.copy_(local)
+            avg = local.clone()
+            dist.all_reduce(avg)
+            avg /= world
+            gg = avg + 1e-5 * pr
+            mr = gg.clone() if mr is None else 0.9 * mr + gg
+            pr = pr - 0.01 * mr
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_bucket(b, sgd=(0.01, 0.9, 1e-5, step == 0), algo="twoshot" if n > 4096 else "oneshot")
+            comm.finalize()
+            torch.cuda.synchronize()
+        res["sgd_%d" % n] = (b.p32 - pr).abs().max().item()
+        res["sgd_%d_shadow" % n] = bool(torch.equal(b.shadow, b.p32.to(torch.bfloat16)))
+        res["sgd_%d_grad" % n] = (b.g32 - avg).abs().max().item()
+    # broadcast of arbitrary tensors through the staging window
+    t = [torch.full((1000, 3), float(rank + 1), device=dev), torch.arange(10, device=dev) + 100 * rank]
+    comm.broadcast_(t, src=0)
+    torch.cuda.synchronize()
+    res["bcast"] = bool((t[0] == 1.0).all().item() and (t[1] == torch.arange(10, device=dev)).all().item())
+    return res
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_p2p_collectives_match_nccl(world):
+    _need(world)
+    out = run_ranks(_collectives, world=world, backend="b200", timeout=600)
+    for r in out:
+        for k, v in r.items():
+            if k.endswith("_ident") or k.endswith("_shadow") or k == "bcast":
+                assert v is True, (k, r)
+            elif k.startswith(("oneshot", "twoshot", "multimem")):
+                assert v < 1e-5, (k, v)
+            elif k.startswith("sgd_"):
+                assert v < 1e-5, (k, v)
+
+
+def _ddp_train(rank, world, sync_bn):
+    import copy
+    import torch.distributed as dist
+    import torch.nn as nn
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel, convert_sync_batchnorm
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    base = resnet18()
+    ref = copy.deepcopy(base)
+    if sync_bn:
+        base = convert_sync_batchnorm(base)
+        ref = nn.SyncBatchNorm.convert_sync_batchnorm(ref)
+    base, ref = base.to(dev), ref.to(dev)
+    if rank == 1:
+        with torch.no_grad():
+            base.fc.bias.add_(1.0)   # ctor broadcast from rank 0 must undo this
+    ours = DistributedDataParallel(base, device_ids=[rank])
+    theirs = TorchDDP(ref, device_ids=[rank])
+    o1 = optim.SGD(ours.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
+    o2 = torch.optim.SGD(theirs.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5)
+    crit = CrossEntropyLoss()
+    g = torch.Generator(device=dev).manual_seed(10 + rank)
+    x = torch.randn(32, 3, 32, 32, device=dev, generator=g)
+    y = torch.randint(0, 10, (32,), device=dev, generator=g)
+    l1s, l2s = [], []
+    for _ in range(5):
+        o1.zero_grad()
+        l1 = crit(ours(x), y)
+        l1.backward()
+        o1.step()
+        o2.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = theirs(x)
+        l2 = nn.functional.cross_entropy(out.float(), y)
+        l2.backward()
+        o2.step()
+        l1s.append(l1.item())
+        l2s.append(l2.item())
+    torch.cuda.synchronize()
+    flat = torch.cat([p.detach().reshape(-1) for p in ours.parameters()])
+    other = flat.clone()
+    dist.broadcast(other, 0)
+    log = ours.collective_log()
+    return {"ours": l1s, "theirs": l2s, "ident": bool(torch.equal(flat, other)), "backend": ours.backend,
+            "n_allreduce": len([c for c in log if c[0] == "allreduce"]), "exposed": ours.exposed_comm_ms()}
+
+
+@pytest.mark.parametrize("sync_bn", [False, True])
+def test_ddp_p2p_trains_like_torch_ddp(sync_bn):
+    _need(2)
+    out = run_ranks(_ddp_train, world=2, backend="b200", args=(sync_bn,), timeout=600)
+    for r in out:
+        assert r["backend"] == "p2p"
+        assert r["ident"], "replicas drifted apart"
+        assert r["n_allreduce"] == 15
+        assert r["ours"][-1] < r["ours"][0]
+        assert abs(r["ours"][0] - r["theirs"][0]) < 0.05 * r["theirs"][0], r
+        assert abs(r["ours"][-1] - r["theirs"][-1]) < 0.35 * max(r["theirs"][-1], 0.5), r
+
+
+def _syncbn_stats(rank, world):
+    import torch.distributed as dist
+    import torch.nn as nn
+    from pytorch_distributed_tutorials_b200.ops import native
+    from pytorch_distributed_tutorials_b200.parallel.comm import P2PComm
+    dev = torch.device("cuda", rank)
+    comm = P2PComm(dev, None, 64 << 20)
+    xg = comm.window.ctx(P2PComm.PAD_COMPUTE)
+    slot = comm.window.alloc(4 * (2 * 2048 + 256)) // 4
+    out = {}
+    for C, H, N in [(64, 9, 3 + rank), (512, 5, 2), (2048, 3, 4)]:
+        torch.manual_seed(100 + rank)
+        y = (torch.randn(N, C, H, H, device=dev) * (1 + rank) + rank).to(torch.bfloat16).contiguous(
+            memory_format=torch.channels_last)
+        gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+        dist.broadcast(gamma, 0)
+        dist.broadcast(beta, 0)
+        rm, rv, nbt = torch.zeros(C, device=dev), torch.ones(C, device=dev), torch.tensor(0, device=dev)
+        mean, invstd = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        ss, coef = torch.empty(2 * C, device=dev), torch.empty(3 * C, device=dev)
+        z = native.bn_fwd_train(y, None, gamma, beta, rm, rv, nbt, 0.1, 1e-5, True, mean, invstd, ss, xg, slot)
+        ref = nn.SyncBatchNorm(C).to(dev)
+        with torch.no_grad():
+            ref.weight.copy_(gamma)
+            ref.bias.copy_(beta)
+        yf = y.float().requires_grad_(True)
+        zr = torch.relu(ref(yf))
+        out["fwd_%d" % C] = ((z.float() - zr).abs().max() / zr.abs().max()).item()
+        out["rm_%d" % C] = (rm - ref.running_mean).abs().max().item()
+        out["rv_%d" % C] = ((rv - ref.running_var).abs().max() / ref.running_var.abs().max()).item()
+        dz = torch.randn_like(zr).to(torch.bfloat16)
+        dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        dy, _ = native.bn_bwd(dz, None, z, y, gamma, mean, invstd, dg, db, False, True, coef, False, xg, slot)
+        zr.backward(dz.float() * (z.float() > 0) / 1.0)
+        out["bwd_%d" % C] = ((dy.float() - yf.grad).abs().max() / yf.grad.abs().max()).item()
+        out["dg_%d" % C] = ((dg - ref.weight.grad).abs().max() / ref.weight.grad.abs().max()).item()
+        torch.cuda.synchronize()
+        dist.barrier()
+    return out
+
+
+def test_syncbn_in_kernel_stats_match_torch():
+    _need(2)
+    outs = run_ranks(_syncbn_stats, world=2, backend="b200", timeout=600)
+    for r in outs:
+        for k, v in r.items():
+            assert v < 3e-2, (k, v, r)
