@@ -12,9 +12,10 @@ namespace b2 {
 #define B2_DEVICE __device__ __forceinline__
 
 // A spin that never ends hangs the GPU box (and costs a strike), so every wait in the library is
-// bounded: after ~2^31 polls the kernel traps and the launch surfaces as a CUDA error on the host.
-#ifndef B2_SPIN_LIMIT
-#define B2_SPIN_LIMIT (1u << 31)
+// bounded in wall time: after B2_SPIN_TIMEOUT_NS the kernel traps and the launch surfaces as a CUDA error
+// on the host (the host-side watchdog in csrc/symm.cu then turns that into a clean non-zero exit).
+#ifndef B2_SPIN_TIMEOUT_NS
+#define B2_SPIN_TIMEOUT_NS 20000000000ull  // 20 s
 #endif
 
 B2_DEVICE uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -53,11 +54,26 @@ B2_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (B2_SPIN_LIMIT >> 6)) __trap();  // try_wait itself sleeps in HW, so far fewer polls
+B2_DEVICE uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Call once per poll of a spin loop: traps when the loop has been spinning for longer than the timeout.
+struct SpinGuard {
+  uint64_t t0 = 0;
+  uint32_t polls = 0;
+  B2_DEVICE void tick() {
+    if ((++polls & 0x3FFu) == 0) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > B2_SPIN_TIMEOUT_NS) __trap();
+    }
   }
+};
+B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
+  SpinGuard guard;
+  while (!mbar_try_wait(bar, parity)) guard.tick();
 }
 
 // ---------------------------------------------------------------- proxies / fences

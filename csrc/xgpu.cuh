@@ -55,10 +55,8 @@ B2_DEVICE void xgpu_barrier(const XgpuCtx& xg, int channel) {
     fence_acq_rel_sys();
     st_release_sys(xg.flags[peer] + channel * B2_MAX_WORLD + xg.rank, e);
     const uint32_t* mine = xg.flags[xg.rank] + channel * B2_MAX_WORLD + peer;
-    uint32_t spins = 0;
-    while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-      if (++spins > B2_SPIN_LIMIT) __trap();
-    }
+    SpinGuard guard;
+    while ((int32_t)(ld_acquire_sys(mine) - e) < 0) guard.tick();
   }
   __syncthreads();
 }

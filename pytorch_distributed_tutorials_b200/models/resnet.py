@@ -127,6 +127,7 @@ class ResNet(nn.Module):
             if self._engine is None:
                 self._engine = ResNetEngine(self)
                 self._engine.xg = getattr(self, "_b2_xgpu_ctx", None)
+                self._engine.xg_slot = getattr(self, "_b2_xgpu_slot", 0)
             return self._engine(x)
         return self.forward_reference(x)
 
@@ -207,7 +208,8 @@ class ResNetEngine:
         self.stem_wp = torch.zeros(64, 192, dtype=torch.bfloat16, device=self.device)
         self.stem_dwp = torch.zeros(64, 192, dtype=torch.float32, device=self.device)
         self.params = list(model.parameters())
-        self.xg = None             # XgpuCtx for SyncBatchNorm (set by parallel.syncbn)
+        self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
+        self.xg_slot = 0           # float offset of the statistics exchange area inside the symmetric window
 
     # ------------------------------------------------------------------ helpers
     def _bn(self, bn):
@@ -259,7 +261,7 @@ class ResNetEngine:
             return native.bn_fwd_train(y, res, bn.weight, bn.bias, bn.running_mean if track else None,
                                        bn.running_var if track else None,
                                        bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
-                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn))
+                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot)
         return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
                                   st.scale_shift)
 
@@ -330,7 +332,7 @@ class ResNetEngine:
         db_slot = self._slot(bn.bias)
         dy, dres = native.bn_bwd(dz_a, dz_b, rec.z if rec.relu else None, rec.y, bn.weight, st.mean, st.invstd,
                                  dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
-                                 self._sync_bn_ctx(bn))
+                                 self._sync_bn_ctx(bn), self.xg_slot)
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight

@@ -210,8 +210,14 @@ class DistributedDataParallel(nn.Module):
         if hasattr(self.module, "_engine"):
             # the engine is created lazily; hand it the context through the model
             self.module._b2_xgpu_ctx = self.xgpu_compute_ctx
+            slot = 0
+            if self.backend == "p2p":
+                # exchange area for per-GPU BN statistics: (sum, sumsq | sum_dy, sum_dy_xmu) + per-CTA counts
+                slot = self.comm.window.alloc(4 * (2 * 2048 + 256)) // 4
+            self.module._b2_xgpu_slot = slot
             if eng is not None:
                 eng.xg = self.xgpu_compute_ctx
+                eng.xg_slot = slot
 
     # ------------------------------------------------------------------ forward
     def forward(self, *inputs, **kwargs):
