@@ -30,6 +30,7 @@ struct ConvParams {
   int Kpix;     // wgrad: number of pixels (K extent)
   int splits;   // wgrad: split-K factor
   int kb_per_split;
+  int im2col_pad;  // TMA im2col: padding of the (possibly transposed) convolution the descriptor encodes
   int tapC;     // channels per tap in the weight's K axis (= Cin): column offset of a tap in W2d
   const float* bias;  // fprop only, optional: added per output column (classifier)
   void* out;    // fprop/dgrad: bf16 [M, Ncols]; wgrad: fp32 workspace [splits][Cout][taps*Cin]
@@ -62,7 +63,11 @@ B2_DEVICE void decode_pix(int p, int PH, int PW, int& n, int& h, int& w) {
   w = r - h * PW;
 }
 
-template <int KIND, bool GATHER, int BN>
+// AMODE: how the activation operand is staged. 0 = tiled TMA (pure GEMM), 1 = cp.async gather by the producer
+// warps, 2 = TMA im2col (the hardware walks the output pixels and applies the filter-tap offset).
+enum { ACT_TILED = 0, ACT_GATHER = 1, ACT_IM2COL = 2 };
+
+template <int KIND, int AMODE, int BN>
 __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
     igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const ConvParams p) {
@@ -92,6 +97,8 @@ __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
   const int nkb = kb_end - kb_begin;
 
   // Which operand (if any) the gather warps fill: fprop/dgrad -> A, wgrad -> B.
+  constexpr bool GATHER = (AMODE == ACT_GATHER);
+  constexpr bool IM2COL = (AMODE == ACT_IM2COL);
   constexpr bool kGatherA = GATHER && (KIND != WGRAD);
   constexpr bool kGatherB = GATHER && (KIND == WGRAD);
   constexpr uint32_t kTmaBytes = (kGatherA ? 0 : C::kABytes) + (kGatherB ? 0 : C::kBBytes);
@@ -117,6 +124,15 @@ __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
   if (warp == 4) {
     // ===================================================== TMA producer (one lane)
     if (lane == 0) {
+      // im2col: base coordinates of this tile's first output pixel in the source tensor (fprop/dgrad)
+      int iw0 = 0, ih0 = 0, in0 = 0;
+      if (IM2COL && KIND != WGRAD) {
+        int n, h, w;
+        decode_pix(m0, p.rowH, p.rowW, n, h, w);
+        in0 = n;
+        ih0 = h * p.stride - p.im2col_pad;
+        iw0 = w * p.stride - p.im2col_pad;
+      }
       for (int i = 0; i < nkb; ++i) {
         const int kb = kb_begin + i;
         const int s = i % C::kStages;
@@ -126,11 +142,23 @@ __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
         uint8_t* sB = sA + C::kABytes;
         mbar_arrive_expect_tx(&full[s], kTmaBytes);
         if (KIND == FPROP) {
-          if (!kGatherA) tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // x2d [M][Cin], box {64,128}
+          if (IM2COL) {
+            const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
+            const int kh = tp / p.KW, kw = tp - kh * p.KW;
+            tma_load_im2col(sA, &tmA, &full[s], cb * 64, iw0, ih0, in0, (uint16_t)kw, (uint16_t)kh);
+          } else if (!kGatherA) {
+            tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // x2d [M][Cin], box {64,128}
+          }
           tma_load_2d(sB, &tmB, &full[s], kb * BK, n0);                 // W2d [Cout][K], box {64,BN}
         } else if (KIND == DGRAD) {
-          if (!kGatherA) tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // dy2d [M][Cout], box {64,128}
           const int t = kb / p.cpb, cob = kb - t * p.cpb;
+          if (IM2COL) {  // stride-1 dgrad == correlation of dy with the flipped filter, pad' = K-1-pad
+            const int kh = t / p.KW, kw = t - kh * p.KW;
+            tma_load_im2col(sA, &tmA, &full[s], cob * 64, iw0, ih0, in0, (uint16_t)(p.KW - 1 - kw),
+                            (uint16_t)(p.KH - 1 - kh));
+          } else if (!kGatherA) {
+            tma_load_2d(sA, &tmA, &full[s], kb * BK, m0);  // dy2d [M][Cout], box {64,128}
+          }
 #pragma unroll
           for (int j = 0; j < BN / 64; ++j)  // W2d [Cout][taps*Cin], box {64 cin, 64 cout} -> MN-major B
             tma_load_2d(sB + j * 8192, &tmB, &full[s], t * p.tapC + n0 + 64 * j, cob * 64);
@@ -138,7 +166,15 @@ __global__ void __launch_bounds__(kThreads, (BN <= 128) ? 2 : 1)
 #pragma unroll
           for (int j = 0; j < 2; ++j)  // dy2d [pixels][Cout], box {64 cout, 64 pixels} -> MN-major A
             tma_load_2d(sA + j * 8192, &tmA, &full[s], m0 + 64 * j, kb * BK);
-          if (!kGatherB) {
+          if (IM2COL) {  // x rows for this tap: 64 output pixels starting at kb*64, 64 channels per box
+            int n, h, w;
+            decode_pix(kb * BK, p.rowH, p.rowW, n, h, w);
+            const int kh = tap / p.KW, kw = tap - kh * p.KW;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_im2col(sB + j * 8192, &tmB, &full[s], n0 + 64 * j, w * p.stride - p.im2col_pad,
+                              h * p.stride - p.im2col_pad, n, (uint16_t)kw, (uint16_t)kh);
+          } else if (!kGatherB) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)  // x2d [pixels][Cin]
               tma_load_2d(sB + j * 8192, &tmB, &full[s], n0 + 64 * j, kb * BK);
@@ -342,10 +378,10 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
   *reinterpret_cast<float4*>(dw + i) = acc;
 }
 
-template <int KIND, bool GATHER, int BN>
+template <int KIND, int AMODE, int BN>
 static cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, dim3 grid,
                           cudaStream_t st) {
-  auto kern = igemm_kernel<KIND, GATHER, BN>;
+  auto kern = igemm_kernel<KIND, AMODE, BN>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
@@ -356,13 +392,13 @@ static cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   return cudaGetLastError();
 }
 
-template <int KIND, bool GATHER>
+template <int KIND, int AMODE>
 static cudaError_t launch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, dim3 grid,
                              cudaStream_t st) {
   switch (bn) {
-    case 64: return launch<KIND, GATHER, 64>(tmA, tmB, p, grid, st);
-    case 128: return launch<KIND, GATHER, 128>(tmA, tmB, p, grid, st);
-    case 256: return launch<KIND, GATHER, 256>(tmA, tmB, p, grid, st);
+    case 64: return launch<KIND, AMODE, 64>(tmA, tmB, p, grid, st);
+    case 128: return launch<KIND, AMODE, 128>(tmA, tmB, p, grid, st);
+    case 256: return launch<KIND, AMODE, 256>(tmA, tmB, p, grid, st);
   }
   return cudaErrorInvalidValue;
 }
@@ -374,12 +410,33 @@ static int pick_bn(int ncols, int force) {
 }
 
 static int g_force_bn = 0;
+static int g_act_mode = -1;  // -1 auto, else force ACT_GATHER / ACT_IM2COL for k>1 or strided convs
+
+template <int KIND>
+static cudaError_t launch_mode(int mode, int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
+                               dim3 grid, cudaStream_t st) {
+  switch (mode) {
+    case ACT_TILED: return launch_bn<KIND, ACT_TILED>(bn, tmA, tmB, p, grid, st);
+    case ACT_GATHER: return launch_bn<KIND, ACT_GATHER>(bn, tmA, tmB, p, grid, st);
+    case ACT_IM2COL: return launch_bn<KIND, ACT_IM2COL>(bn, tmA, tmB, p, grid, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+// Staging mode for the activation operand of a (KH,KW,stride,pad) convolution.
+static int pick_mode(int kind, int KH, int KW, int stride, int pad) {
+  if (KH == 1 && KW == 1 && stride == 1 && pad == 0) return ACT_TILED;
+  if (g_act_mode == ACT_GATHER) return ACT_GATHER;
+  if (kind == DGRAD && stride != 1) return ACT_GATHER;  // strided dgrad has holes the im2col walk cannot skip
+  return ACT_IM2COL;
+}
 
 }  // namespace b2
 
 using namespace b2;
 
 extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
+extern "C" void b2_conv_set_act_mode(int mode) { g_act_mode = mode; }
 
 extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
                              int Cout, int KH, int KW, int stride, int pad, void* stream) {
@@ -387,20 +444,26 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, vo
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * Ho * Wo, K = KH * KW * Cin;
   const int bn = pick_bn(Cout, g_force_bn);
-  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  const int mode = pick_mode(FPROP, KH, KW, stride, pad);
   CUtensorMap tmA, tmB;
   int e;
-  // A: x2d [M][Cin] (only dereferenced on the pure-GEMM path); B: W2d [Cout][K], box {64, bn}
-  if ((e = make_tmap_2d_bf16(&tmA, x, (uint64_t)Cin, (uint64_t)(gather ? N * H * W : M), 64, 128))) return e;
+  // A: x2d [M][Cin] on the pure-GEMM path, im2col view of x otherwise; B: W2d [Cout][K], box {64, bn}
+  if (mode == ACT_IM2COL) {
+    if ((e = make_tmap_im2col_bf16(&tmA, x, N, H, W, Cin, -pad, -pad, pad - (KW - 1), pad - (KH - 1), 64, 128,
+                                   stride)))
+      return e;
+  } else if ((e = make_tmap_2d_bf16(&tmA, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 128))) {
+    return e;
+  }
   if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)K, (uint64_t)Cout, 64, bn))) return e;
   ConvParams p{};
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cout; p.Kblocks = K / 64; p.cpb = Cin / 64; p.tapC = Cin;
-  p.out = y; p.out_ld = Cout; p.splits = 1; p.bias = bias;
+  p.out = y; p.out_ld = Cout; p.splits = 1; p.bias = bias; p.im2col_pad = pad;
   dim3 grid((Cout + bn - 1) / bn, (M + BM - 1) / BM, 1);
   cudaStream_t st = (cudaStream_t)stream;
-  return gather ? launch_bn<FPROP, true>(bn, tmA, tmB, p, grid, st) : launch_bn<FPROP, false>(bn, tmA, tmB, p, grid, st);
+  return launch_mode<FPROP>(mode, bn, tmA, tmB, p, grid, st);
 }
 
 extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
@@ -410,19 +473,27 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   const int M = N * H * W;
   const int cpb = (Cout + 63) / 64;
   const int bn = pick_bn(Cin, g_force_bn);
-  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  const int mode = pick_mode(DGRAD, KH, KW, stride, pad);
   CUtensorMap tmA, tmB;
   int e;
-  if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) return e;
+  if (mode == ACT_IM2COL) {  // dy viewed through the transposed convolution: pad' = K-1-pad, stride 1
+    const int pw = KW - 1 - pad, phh = KH - 1 - pad;
+    if (pw != phh) return cudaErrorInvalidValue;
+    if ((e = make_tmap_im2col_bf16(&tmA, dy, N, Ho, Wo, Cout, -pw, -phh, pw - (KW - 1), phh - (KH - 1), 64, 128, 1)))
+      return e;
+  } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) {
+    return e;
+  }
   if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) return e;
   ConvParams p{};
   p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
   p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cin; p.Kblocks = KH * KW * cpb; p.cpb = cpb; p.tapC = Cin;
-  p.out = dx; p.out_ld = Cin; p.splits = 1;
+  p.out = dx; p.out_ld = Cin; p.splits = 1; p.im2col_pad = KW - 1 - pad;
+  if (mode == ACT_IM2COL) p.stride = 1;
   dim3 grid(Cin / bn, (M + BM - 1) / BM, 1);
   cudaStream_t st = (cudaStream_t)stream;
-  return gather ? launch_bn<DGRAD, true>(bn, tmA, tmB, p, grid, st) : launch_bn<DGRAD, false>(bn, tmA, tmB, p, grid, st);
+  return launch_mode<DGRAD>(mode, bn, tmA, tmB, p, grid, st);
 }
 
 // Split-K plan for wgrad: enough CTAs for ~2 waves of 148 SMs x 2 resident CTAs, bounded by the workspace.
@@ -450,7 +521,7 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
   const int bn = pick_bn(Cin, g_force_bn);
-  const bool gather = !(KH == 1 && KW == 1 && stride == 1 && pad == 0);
+  const int mode = pick_mode(WGRAD, KH, KW, stride, pad);
   const long long wcount = (long long)Cout * taps * Cin;
   if (ws_bytes < wcount * 4) return cudaErrorInvalidValue;
   const int splits = b2_conv_wgrad_splits(N, Ho, Wo, Cin, Cout, taps, ws_bytes);
@@ -458,17 +529,21 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   CUtensorMap tmA, tmB;
   int e;
   if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, 64))) return e;
-  if ((e = make_tmap_2d_bf16(&tmB, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 64))) return e;
+  if (mode == ACT_IM2COL) {
+    if ((e = make_tmap_im2col_bf16(&tmB, x, N, H, W, Cin, -pad, -pad, pad - (KW - 1), pad - (KH - 1), 64, 64, stride)))
+      return e;
+  } else if ((e = make_tmap_2d_bf16(&tmB, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 64))) {
+    return e;
+  }
   ConvParams p{};
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
-  p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad; p.im2col_pad = pad;
   p.M = Cout; p.Ncols = Cin; p.Kblocks = kblocks; p.Kpix = (int)kpix; p.tapC = Cin;
   p.splits = splits; p.kb_per_split = per;
   p.out = workspace; p.out_ld = (long long)taps * Cin; p.split_stride = wcount;
   dim3 grid(Cin / bn, (Cout + BM - 1) / BM, taps * splits);
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t ce = gather ? launch_bn<WGRAD, true>(bn, tmA, tmB, p, grid, st)
-                          : launch_bn<WGRAD, false>(bn, tmA, tmB, p, grid, st);
+  cudaError_t ce = launch_mode<WGRAD>(mode, bn, tmA, tmB, p, grid, st);
   if (ce != cudaSuccess) return ce;
   const int thr = 256;
   const long long nvec = (wcount + 3) / 4;

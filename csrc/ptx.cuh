@@ -92,6 +92,18 @@ B2_DEVICE void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, 
       : "memory");
 }
 
+// TMA im2col load (NHWC): `pixelsPerColumn` consecutive output positions starting at base pixel (w,h,n), channels
+// [c, c+channelsPerPixel), each displaced by the filter-tap offset (off_w, off_h); padding reads as zero.
+B2_DEVICE void tma_load_im2col(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
+                               uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h),
+      "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+
 // ---------------------------------------------------------------- cp.async (LDGSTS) with zero-fill
 B2_DEVICE void cp_async16(uint32_t smem_dst, const void* gsrc, uint32_t src_bytes /*0 or 16*/) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(src_bytes)

@@ -9,4 +9,8 @@ namespace b2 {
 // Returns 0 on success, a CUresult/cudaError value otherwise.
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint32_t box_inner,
                       uint32_t box_outer);
+// im2col view of an NHWC bf16 tensor [N][H][W][C] (128B swizzle, zero fill): boxes of `channels` x `pixels`,
+// bounding box corners as in cuTensorMapEncodeIm2col (lower = -pad, upper = pad - (K-1)*dilation), traversal stride.
+int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int N, int H, int W, int C, int lower_w, int lower_h,
+                          int upper_w, int upper_h, int channels, int pixels, int stride);
 }  // namespace b2

@@ -47,6 +47,8 @@ int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, lo
 int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes);
 /* Debug/tuning: force the N tile (64/128/256); 0 = automatic. */
 void b2_conv_set_tile_n(int bn);
+/* Debug/tuning: staging of k>1 / strided activations: -1 auto (TMA im2col), 1 = cp.async gather. */
+void b2_conv_set_act_mode(int mode);
 
 /* ------------------------------------------------------------------------------------------------
  * BatchNorm (+ReLU, +residual add) forward/backward on NHWC bf16, fp32 statistics (csrc/bn.cu).
