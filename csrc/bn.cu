@@ -10,6 +10,9 @@
 #include "ptx.cuh"
 #include "xgpu.cuh"
 
+#include <cstdio>
+#include <mutex>
+
 namespace b2 {
 
 constexpr int kBnThreads = 256;
@@ -435,4 +438,61 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
   B2_BWD_DISPATCH(APP, 0);
 #undef APP
   return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// Training-mode BatchNorm forward for callers that must not allocate device memory: a stream that is being
+// captured into a CUDA graph, a latency-critical loop where cudaMalloc's implicit device synchronisation is not
+// acceptable, or a host application that hands this library a fixed memory budget and forbids side allocations.
+// The per-CTA partial sums (the only scratch the BN forward needs) live in a file-scope device array instead of a
+// caller-provided buffer.  The array is sized for the widest layer the library supports and exists once per GPU
+// that loads the library, for the lifetime of the process.
+constexpr int kNoAllocMaxChannels = B2_BN_NOALLOC_MAX_CHANNELS;
+static __device__ __align__(256) float g_bn_noalloc_scratch[(size_t)b2::kMaxPartialBlocks * 2 * kNoAllocMaxChannels];
+
+// Device address of the scratch array for the current device.  In host code the array's name is only a handle for
+// the runtime, not something a kernel can dereference, so the address is looked up once per device (with that
+// device current) and cached.
+static cudaError_t bn_noalloc_scratch(float** out) {
+  static std::mutex mu;
+  static float* ptrs[64] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> g(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_bn_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return cudaSuccess;
+}
+
+extern "C" int b2_bn_fwd_train_noalloc(const void* y, const void* res, void* z, long long M, int C,
+                                       const float* gamma, const float* beta, float* running_mean,
+                                       float* running_var, long long* num_batches_tracked, float momentum, float eps,
+                                       int relu, float* mean, float* invstd, float* scale_shift,
+                                       const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  if (C > kNoAllocMaxChannels) {
+    std::fprintf(stderr,
+                 "b2_bn_fwd_train_noalloc: C=%d exceeds the built-in scratch (B2_BN_NOALLOC_MAX_CHANNELS=%d); use "
+                 "b2_bn_fwd_train with a caller-provided partial buffer\n",
+                 C, kNoAllocMaxChannels);
+    return cudaErrorInvalidValue;
+  }
+  if (!bn_shape_ok(C) || M <= 0) {
+    std::fprintf(stderr, "b2_bn_fwd_train_noalloc: unsupported shape M=%lld C=%d (C must divide 2048 and be >= 8)\n",
+                 M, C);
+    return cudaErrorInvalidValue;
+  }
+  float* scratch = nullptr;
+  cudaError_t e = bn_noalloc_scratch(&scratch);
+  if (e != cudaSuccess) return e;
+  // Nothing in the scratch has to start at zero: the statistics kernel overwrites every partial the finalize
+  // kernel reads, so whatever the previous call left behind is never observed.
+  return b2_bn_fwd_train(y, res, z, M, C, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps,
+                         relu, mean, invstd, scale_shift, scratch, xg, xg_slot, stream);
 }

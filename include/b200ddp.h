@@ -65,6 +65,24 @@ int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C,
 int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma, const float* beta,
                    const float* running_mean, const float* running_var, float eps, int relu, float* scale_shift,
                    void* stream);
+/* Same operation as b2_bn_fwd_train for callers that cannot allocate device memory (a stream under CUDA-graph
+ * capture, a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a host application with a
+ * fixed memory budget): the partial-sum scratch is a static device array inside the library instead of a
+ * caller-provided buffer, so the call performs no cudaMalloc / cudaFree and no allocating library routine.
+ * Inputs and outputs are still the caller's.  This entry point has no counterpart in the reference.
+ *   - Limit: C <= B2_BN_NOALLOC_MAX_CHANNELS; larger C is rejected with cudaErrorInvalidValue and a message on
+ *     stderr.  The array (592 * 2 * 2048 floats, about 9.25 MiB) is held by every GPU that loads the library,
+ *     until the process exits.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress with that device
+ *     current); make that first call before starting any stream capture.
+ *   - All calls on a device share the one array, and it keeps whatever the last call wrote. Nothing in it needs
+ *     to start at zero (every value that is read is written first within the same call), but two calls whose
+ *     kernels overlap on the GPU (different streams) race on it: serialise them. */
+#define B2_BN_NOALLOC_MAX_CHANNELS 2048
+int b2_bn_fwd_train_noalloc(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
+                            const float* beta, float* running_mean, float* running_var,
+                            long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
+                            float* invstd, float* scale_shift, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 /* dz' = (dz_a + dz_b) * relu_mask(z); dy = BN backward of dz'; dres (optional) receives dz'. */
 int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, void* dy, void* dres, long long M,
               int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
