@@ -441,9 +441,9 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
 }
 
 // ------------------------------------------------------------------------------------------------ no-allocation variant
-// Training-mode BatchNorm forward for callers that must not allocate device memory: a stream that is being
-// captured into a CUDA graph, a latency-critical loop where cudaMalloc's implicit device synchronisation is not
-// acceptable, or a host application that hands this library a fixed memory budget and forbids side allocations.
+// Training-mode BatchNorm forward for callers that must not allocate device memory: a latency-critical loop where
+// cudaMalloc's implicit device synchronisation is not acceptable, a host application that hands this library a
+// fixed memory budget and forbids side allocations, or a GPU so full that an allocation could fail mid-step.
 // The per-CTA partial sums (the only scratch the BN forward needs) live in a file-scope device array instead of a
 // caller-provided buffer.  The array is sized for the widest layer the library supports and exists once per GPU
 // that loads the library, for the lifetime of the process.

@@ -65,9 +65,9 @@ int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C,
 int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma, const float* beta,
                    const float* running_mean, const float* running_var, float eps, int relu, float* scale_shift,
                    void* stream);
-/* Same operation as b2_bn_fwd_train for callers that cannot allocate device memory (a stream under CUDA-graph
- * capture, a serving loop that cannot afford cudaMalloc's device-wide synchronisation, a host application with a
- * fixed memory budget): the partial-sum scratch is a static device array inside the library instead of a
+/* Same operation as b2_bn_fwd_train for callers that cannot allocate device memory (a serving loop that cannot
+ * afford cudaMalloc's device-wide synchronisation, a host application that owns the memory budget and forbids
+ * side allocations, a GPU so full that an allocation could fail mid-step): the partial-sum scratch is a static device array inside the library instead of a
  * caller-provided buffer, so the call performs no cudaMalloc / cudaFree and no allocating library routine.
  * Inputs and outputs are still the caller's.  This entry point has no counterpart in the reference.
  *   - Limit: C <= B2_BN_NOALLOC_MAX_CHANNELS; larger C is rejected with cudaErrorInvalidValue and a message on

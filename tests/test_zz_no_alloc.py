@@ -1,8 +1,8 @@
 """The allocation-free BatchNorm entry point, called through the C ABI exactly as an external caller would.
 
-Some users of this library drive it from places where device memory cannot be allocated: inside a region that is
-being captured into a CUDA graph, from a serving loop that cannot tolerate the device-wide synchronisation a
-cudaMalloc implies, or from a host program that owns the whole memory budget.  ``b2_bn_fwd_train_noalloc`` keeps
+Some users of this library drive it from places where device memory cannot be allocated: from a serving loop that
+cannot tolerate the device-wide synchronisation a cudaMalloc implies, from a host program that owns the whole
+memory budget, or on a GPU that is already nearly full.  ``b2_bn_fwd_train_noalloc`` keeps
 the kernel's scratch in a static device array for them.  This test checks that it computes what the regular entry
 point (``b2_bn_fwd_train`` with a caller-provided scratch buffer) computes, on two calls in a row with different
 shapes (so stale scratch contents from the first call are visible to the second if they mattered), and that a
