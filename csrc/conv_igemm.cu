@@ -36,6 +36,13 @@ struct ConvParams {
   void* out;    // fprop/dgrad: bf16 [M, Ncols]; wgrad: fp32 workspace [splits][Cout][taps*Cin]
   long long out_ld;
   long long split_stride;  // wgrad: elements between split slabs
+  // ---- persistent kernel (v2)
+  int n_tiles, m_tiles, taps;      // work-item grid: item -> (n tile fastest, m tile, tap, split)
+  int im2col_pad_h, im2col_pad_w;  // = -lower corner of the im2col bounding box
+  // dgrad tap walk: kh = kh0 + kstep*th (th < nth), same for w. Strided dgrad runs once per output-pixel parity
+  // class (ph, pw): rows enumerate the class grid [N, rowH, rowW] and land on pixel (cls*i+ph, cls*j+pw) of dx.
+  int kh0, kw0, kstep, nth, ntw;
+  int cls, ph, pw, outH, outW;
 };
 
 constexpr int BM = 128;
@@ -431,6 +438,298 @@ static int pick_mode(int kind, int KH, int KW, int stride, int pad) {
   return ACT_IM2COL;
 }
 
+
+// =====================================================================================================
+// v2: persistent, TMEM double-buffered.  One CTA per SM loops over work items; while the four epilogue warps drain
+// accumulator stage t&1 (TMEM -> registers -> bf16 -> global), the MMA warp is already accumulating the next item
+// into the other stage and the TMA warp is several k-blocks ahead.  Activation staging is TMA only (tiled for
+// pure GEMMs, im2col otherwise); strided dgrad is decomposed into output-pixel parity classes so that the im2col
+// walk never multiplies structural zeros.
+// =====================================================================================================
+constexpr int kThreads2 = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
+
+template <int BN>
+struct Cfg2 {
+  static constexpr int kStageBytes = BM * 128 + BN * 128;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kSmem = kStages * kStageBytes + 1024 + 256;
+};
+
+struct Item {
+  int n0, m0, tap, split, kb_begin, nkb;
+};
+B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn) {
+  Item it;
+  const int nt = item % p.n_tiles;
+  int r = item / p.n_tiles;
+  const int mt = r % p.m_tiles;
+  it.n0 = nt * bn;
+  it.m0 = mt * BM;
+  it.tap = 0; it.split = 0; it.kb_begin = 0; it.nkb = p.Kblocks;
+  if (kind == WGRAD) {
+    const int z = r / p.m_tiles;
+    it.tap = z / p.splits;
+    it.split = z - it.tap * p.splits;
+    it.kb_begin = it.split * p.kb_per_split;
+    it.nkb = min(p.Kblocks, it.kb_begin + p.kb_per_split) - it.kb_begin;
+  }
+  return it;
+}
+
+template <int KIND, int AMODE, int BN>
+__global__ void __launch_bounds__(kThreads2, 1)
+    igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const ConvParams p, int num_items) {
+  using C = Cfg2<BN>;
+  constexpr bool IM2COL = (AMODE == ACT_IM2COL);
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* tfull = bars + 2 * C::kStages;       // [2] accumulator stage ready for the epilogue
+  uint64_t* tempty = bars + 2 * C::kStages + 2;  // [2] accumulator stage drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kABytes = BM * 128, kBBytes = BN * 128;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4);  // one arrival per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) tmem_alloc<2 * BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      uint32_t g = 0;  // global k-block counter (smem ring position carries over from item to item)
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const Item it = decode_item(p, item, KIND, BN);
+        int iw0 = 0, ih0 = 0, in0 = 0;
+        if (IM2COL && KIND != WGRAD) {
+          int n, h, w;
+          decode_pix(it.m0, p.rowH, p.rowW, n, h, w);
+          in0 = n;
+          ih0 = h * p.stride - p.im2col_pad_h;
+          iw0 = w * p.stride - p.im2col_pad_w;
+        }
+        for (int i = 0; i < it.nkb; ++i, ++g) {
+          const int kb = it.kb_begin + i;
+          const int s = g % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sA = smem + s * C::kStageBytes;
+          uint8_t* sB = sA + kABytes;
+          mbar_arrive_expect_tx(&full[s], kABytes + kBBytes);
+          if (KIND == FPROP) {
+            if (IM2COL) {
+              const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
+              const int kh = tp / p.KW, kw = tp - kh * p.KW;
+              tma_load_im2col(sA, &tmA, &full[s], cb * 64, iw0, ih0, in0, (uint16_t)kw, (uint16_t)kh);
+            } else {
+              tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
+            }
+            tma_load_2d(sB, &tmB, &full[s], kb * BK, it.n0);
+          } else if (KIND == DGRAD) {
+            const int tp = kb / p.cpb, cob = kb - tp * p.cpb;
+            int tapidx = 0;
+            if (IM2COL) {
+              const int th = tp / p.ntw, tw = tp - th * p.ntw;
+              tapidx = (p.kh0 + p.kstep * th) * p.KW + (p.kw0 + p.kstep * tw);
+              tma_load_im2col(sA, &tmA, &full[s], cob * 64, iw0, ih0, in0, (uint16_t)(p.ntw - 1 - tw),
+                              (uint16_t)(p.nth - 1 - th));
+            } else {
+              tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
+            }
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sB + j * 8192, &tmB, &full[s], tapidx * p.tapC + it.n0 + 64 * j, cob * 64);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
+            if (IM2COL) {
+              int n, h, w;
+              decode_pix(kb * BK, p.rowH, p.rowW, n, h, w);
+              const int kh = it.tap / p.KW, kw = it.tap - kh * p.KW;
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_im2col(sB + j * 8192, &tmB, &full[s], it.n0 + 64 * j, w * p.stride - p.im2col_pad_w,
+                                h * p.stride - p.im2col_pad_h, n, (uint16_t)kw, (uint16_t)kh);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(sB + j * 8192, &tmB, &full[s], it.n0 + 64 * j, kb * BK);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      constexpr bool kAmn = (KIND == WGRAD);
+      constexpr bool kBmn = (KIND != FPROP);
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, kAmn, kBmn);
+      uint32_t g = 0, t = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
+        const Item it = decode_item(p, item, KIND, BN);
+        const uint32_t acc = t & 1;
+        mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);  // epilogue has drained this accumulator stage
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int i = 0; i < it.nkb; ++i, ++g) {
+          const int s = g % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t aBase = smem_u32(smem + s * C::kStageBytes);
+          const uint32_t bBase = aBase + kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = kAmn ? make_smem_desc_sw128(aBase + k * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(aBase + k * 32, 16, 1024);
+            const uint64_t db = kBmn ? make_smem_desc_sw128(bBase + k * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(bBase + k * 32, 16, 1024);
+            umma_bf16(d_tmem, da, db, idesc, (i | k) != 0);
+          }
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else {
+    // ===================================================== epilogue warps 2..5 (TMEM lane quadrant = warp % 4)
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    uint32_t t = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
+      const Item it = decode_item(p, item, KIND, BN);
+      const uint32_t acc = t & 1;
+      mbar_wait(&tfull[acc], (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
+      const int m = it.m0 + row;
+      const bool ok = m < p.M;
+      if (KIND != WGRAD) {
+        long long orow_idx = m;
+        if (KIND == DGRAD && p.cls > 1 && ok) {
+          int n, i, j;
+          decode_pix(m, p.rowH, p.rowW, n, i, j);
+          orow_idx = ((long long)n * p.outH + (i * p.cls + p.ph)) * p.outW + (j * p.cls + p.pw);
+        }
+        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_ld + it.n0;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int col = it.n0 + c * 32 + q * 8;
+              if (col + 8 > p.Ncols) break;
+              if (p.bias) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
+              }
+              uint4 o;
+              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              st_v4(orow + c * 32 + q * 8, o);
+            }
+          }
+        }
+      } else {
+        float* out = reinterpret_cast<float*>(p.out) + (size_t)it.split * p.split_stride;
+        float* orow = out + (size_t)m * p.out_ld + (size_t)it.tap * p.tapC + it.n0;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+          }
+        }
+      }
+      // release the accumulator stage: all of this warp's TMEM reads have completed (wait::ld above)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_free<2 * BN>(tmem_base);
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <int KIND, int AMODE, int BN>
+static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int items,
+                           cudaStream_t st) {
+  auto kern = igemm2_kernel<KIND, AMODE, BN>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::kSmem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const int grid = items < num_sms() ? items : num_sms();
+  kern<<<grid, kThreads2, Cfg2<BN>::kSmem, st>>>(tmA, tmB, p, items);
+  return cudaGetLastError();
+}
+template <int KIND, int AMODE>
+static cudaError_t launch2_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int items,
+                              cudaStream_t st) {
+  switch (bn) {
+    case 64: return launch2<KIND, AMODE, 64>(tmA, tmB, p, items, st);
+    case 128: return launch2<KIND, AMODE, 128>(tmA, tmB, p, items, st);
+    case 256: return launch2<KIND, AMODE, 256>(tmA, tmB, p, items, st);
+  }
+  return cudaErrorInvalidValue;
+}
+template <int KIND>
+static cudaError_t launch2_mode(int mode, int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
+                                int items, cudaStream_t st) {
+  if (mode == ACT_TILED) return launch2_bn<KIND, ACT_TILED>(bn, tmA, tmB, p, items, st);
+  if (mode == ACT_IM2COL) return launch2_bn<KIND, ACT_IM2COL>(bn, tmA, tmB, p, items, st);
+  return cudaErrorInvalidValue;
+}
+
+static int g_impl = 2;  // 1 = one tile per CTA (v1), 2 = persistent (v2)
 }  // namespace b2
 
 using namespace b2;
@@ -438,12 +737,25 @@ using namespace b2;
 extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
 extern "C" void b2_conv_set_act_mode(int mode) { g_act_mode = mode; }
 
+extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
+
+// N-tile policy (measured on B200, batch 256, tools/conv_check.py): the persistent kernel prefers the widest tile
+// the channel count allows; wgrad only when Cout fills at least two M tiles.
+static int bn_for(int ncols, int kind = FPROP, int m_extent = 1 << 30) {
+  if (g_force_bn) return pick_bn(ncols, g_force_bn);
+  if (g_impl == 2) {
+    const bool wide_ok = (kind != WGRAD) || m_extent >= 256;
+    if (ncols % 256 == 0 && wide_ok) return 256;
+  }
+  return pick_bn(ncols, 0);
+}
+
 extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
                              int Cout, int KH, int KW, int stride, int pad, void* stream) {
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * Ho * Wo, K = KH * KW * Cin;
-  const int bn = pick_bn(Cout, g_force_bn);
+  const int bn = bn_for(Cout);
   const int mode = pick_mode(FPROP, KH, KW, stride, pad);
   CUtensorMap tmA, tmB;
   int e;
@@ -461,9 +773,57 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, vo
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cout; p.Kblocks = K / 64; p.cpb = Cin / 64; p.tapC = Cin;
   p.out = y; p.out_ld = Cout; p.splits = 1; p.bias = bias; p.im2col_pad = pad;
-  dim3 grid((Cout + bn - 1) / bn, (M + BM - 1) / BM, 1);
+  p.im2col_pad_h = pad; p.im2col_pad_w = pad; p.cls = 1; p.taps = KH * KW;
+  p.n_tiles = (Cout + bn - 1) / bn; p.m_tiles = (M + BM - 1) / BM;
   cudaStream_t st = (cudaStream_t)stream;
+  if (g_impl == 2 && mode != ACT_GATHER) return launch2_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<FPROP>(mode, bn, tmA, tmB, p, grid, st);
+}
+
+// Strided dgrad, one output-pixel parity class at a time (persistent kernel + TMA im2col over dy).
+static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                            int KW, int stride, int pad, int Ho, int Wo, int bn, cudaStream_t st) {
+  CUtensorMap tmB;
+  int e;
+  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) return e;
+  const int cpb = (Cout + 63) / 64;
+  bool need_zero = false;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const int kh0 = (ph + pad) % stride, kw0 = (pw + pad) % stride;
+      if (kh0 >= KH || kw0 >= KW || ph >= H || pw >= W) need_zero = true;
+    }
+  if (need_zero) {
+    cudaError_t ce = cudaMemsetAsync(dx, 0, (size_t)N * H * W * Cin * 2, st);
+    if (ce != cudaSuccess) return ce;
+  }
+  for (int ph = 0; ph < stride && ph < H; ++ph) {
+    for (int pw = 0; pw < stride && pw < W; ++pw) {
+      const int kh0 = (ph + pad) % stride, kw0 = (pw + pad) % stride;
+      if (kh0 >= KH || kw0 >= KW) continue;  // no tap reaches this class: dx stays zero
+      const int nth = (KH - kh0 + stride - 1) / stride, ntw = (KW - kw0 + stride - 1) / stride;
+      const int d0h = (ph + pad - kh0) / stride, d0w = (pw + pad - kw0) / stride;
+      const int Hc = (H - ph + stride - 1) / stride, Wc = (W - pw + stride - 1) / stride;
+      const int lower_h = d0h - (nth - 1), lower_w = d0w - (ntw - 1);
+      const int upper_h = Hc - Ho + lower_h, upper_w = Wc - Wo + lower_w;
+      CUtensorMap tmA;
+      if ((e = make_tmap_im2col_bf16(&tmA, dy, N, Ho, Wo, Cout, lower_w, lower_h, upper_w, upper_h, 64, 128, 1)))
+        return e;
+      ConvParams p{};
+      p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
+      p.rowH = Hc; p.rowW = Wc; p.KH = KH; p.KW = KW; p.stride = 1; p.pad = pad;
+      p.M = N * Hc * Wc; p.Ncols = Cin; p.cpb = cpb; p.Kblocks = nth * ntw * cpb; p.tapC = Cin;
+      p.out = dx; p.out_ld = Cin; p.splits = 1;
+      p.im2col_pad_h = -lower_h; p.im2col_pad_w = -lower_w;
+      p.kh0 = kh0; p.kw0 = kw0; p.kstep = stride; p.nth = nth; p.ntw = ntw;
+      p.cls = stride; p.ph = ph; p.pw = pw; p.outH = H; p.outW = W; p.taps = KH * KW;
+      p.n_tiles = Cin / bn; p.m_tiles = (p.M + BM - 1) / BM;
+      cudaError_t ce = launch2_mode<DGRAD>(ACT_IM2COL, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+      if (ce != cudaSuccess) return ce;
+    }
+  }
+  return 0;
 }
 
 extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
@@ -472,13 +832,15 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * H * W;
   const int cpb = (Cout + 63) / 64;
-  const int bn = pick_bn(Cin, g_force_bn);
+  const int bn = bn_for(Cin);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (stride > 1 && g_impl == 2 && g_act_mode != ACT_GATHER && Cout % 64 == 0)
+    return dgrad_strided_v2(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, Ho, Wo, bn, st);
   const int mode = pick_mode(DGRAD, KH, KW, stride, pad);
   CUtensorMap tmA, tmB;
   int e;
   if (mode == ACT_IM2COL) {  // dy viewed through the transposed convolution: pad' = K-1-pad, stride 1
     const int pw = KW - 1 - pad, phh = KH - 1 - pad;
-    if (pw != phh) return cudaErrorInvalidValue;
     if ((e = make_tmap_im2col_bf16(&tmA, dy, N, Ho, Wo, Cout, -pw, -phh, pw - (KW - 1), phh - (KH - 1), 64, 128, 1)))
       return e;
   } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) {
@@ -490,19 +852,22 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cin; p.Kblocks = KH * KW * cpb; p.cpb = cpb; p.tapC = Cin;
   p.out = dx; p.out_ld = Cin; p.splits = 1; p.im2col_pad = KW - 1 - pad;
+  p.im2col_pad_h = KH - 1 - pad; p.im2col_pad_w = KW - 1 - pad;
+  p.kh0 = 0; p.kw0 = 0; p.kstep = 1; p.nth = KH; p.ntw = KW; p.cls = 1; p.outH = H; p.outW = W; p.taps = KH * KW;
   if (mode == ACT_IM2COL) p.stride = 1;
-  dim3 grid(Cin / bn, (M + BM - 1) / BM, 1);
-  cudaStream_t st = (cudaStream_t)stream;
+  p.n_tiles = Cin / bn; p.m_tiles = (M + BM - 1) / BM;
+  if (g_impl == 2 && mode != ACT_GATHER) return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<DGRAD>(mode, bn, tmA, tmB, p, grid, st);
 }
 
-// Split-K plan for wgrad: enough CTAs for ~2 waves of 148 SMs x 2 resident CTAs, bounded by the workspace.
+// Split-K plan for wgrad: enough work items for ~2-4 per SM, bounded by the workspace.
 extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes) {
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
-  const int bn = pick_bn(Cin, g_force_bn);
+  const int bn = bn_for(Cin, WGRAD, Cout);
   const long long tiles = (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
-  long long want = (4 * 148 + tiles - 1) / tiles;
+  long long want = ((g_impl == 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
   const long long wbytes = (long long)Cout * taps * Cin * 4;
   long long cap = ws_bytes / wbytes;
   if (want > cap) want = cap;
@@ -520,7 +885,7 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const int taps = KH * KW;
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
-  const int bn = pick_bn(Cin, g_force_bn);
+  const int bn = bn_for(Cin, WGRAD, Cout);
   const int mode = pick_mode(WGRAD, KH, KW, stride, pad);
   const long long wcount = (long long)Cout * taps * Cin;
   if (ws_bytes < wcount * 4) return cudaErrorInvalidValue;
@@ -538,12 +903,19 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   ConvParams p{};
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad; p.im2col_pad = pad;
+  p.im2col_pad_h = pad; p.im2col_pad_w = pad; p.cls = 1; p.taps = taps;
   p.M = Cout; p.Ncols = Cin; p.Kblocks = kblocks; p.Kpix = (int)kpix; p.tapC = Cin;
   p.splits = splits; p.kb_per_split = per;
   p.out = workspace; p.out_ld = (long long)taps * Cin; p.split_stride = wcount;
-  dim3 grid(Cin / bn, (Cout + BM - 1) / BM, taps * splits);
+  p.n_tiles = Cin / bn; p.m_tiles = (Cout + BM - 1) / BM;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t ce = launch_mode<WGRAD>(mode, bn, tmA, tmB, p, grid, st);
+  cudaError_t ce;
+  if (g_impl == 2 && mode != ACT_GATHER) {
+    ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * taps * splits, st);
+  } else {
+    dim3 grid(p.n_tiles, p.m_tiles, taps * splits);
+    ce = launch_mode<WGRAD>(mode, bn, tmA, tmB, p, grid, st);
+  }
   if (ce != cudaSuccess) return ce;
   const int thr = 256;
   const long long nvec = (wcount + 3) / 4;

@@ -49,6 +49,8 @@ int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, lon
 void b2_conv_set_tile_n(int bn);
 /* Debug/tuning: staging of k>1 / strided activations: -1 auto (TMA im2col), 1 = cp.async gather. */
 void b2_conv_set_act_mode(int mode);
+/* Debug/tuning: 1 = one tile per CTA, 2 = persistent kernel with double-buffered TMEM accumulators (default). */
+void b2_conv_set_impl(int impl);
 
 /* ------------------------------------------------------------------------------------------------
  * BatchNorm (+ReLU, +residual add) forward/backward on NHWC bf16, fp32 statistics (csrc/bn.cu).

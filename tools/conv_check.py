@@ -34,12 +34,14 @@ def main():
     ap.add_argument("--limit", type=int, default=0)
     ap.add_argument("--time", action="store_true")
     ap.add_argument("--act-mode", type=int, default=-1)
+    ap.add_argument("--impl", type=int, default=2)
     ap.add_argument("--shape", default=None, help="ci,co,k,s,p,H: run only this shape")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
     _lib.lib().b2_conv_set_tile_n(a.bn)
     _lib.lib().b2_conv_set_act_mode(a.act_mode)
+    _lib.lib().b2_conv_set_impl(a.impl)
     shapes = SHAPES[: a.limit] if a.limit else SHAPES
     if a.shape:
         shapes = [tuple(int(v) for v in a.shape.split(','))]
