@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
                                                        const __nv_bfloat16* __restrict__ res,
                                                        const float* __restrict__ scale,
                                                        const float* __restrict__ shift, __nv_bfloat16* __restrict__ z,
-                                                       long long nvec, int C8) {
+                                                       unsigned char* __restrict__ mask, long long nvec, int C8) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
        i += (long long)gridDim.x * blockDim.x) {
     const int cv = (int)(i % C8);
@@ -198,6 +198,12 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
       for (int j = 0; j < 8; ++j) o.v[j] = fmaf(v.v[j], sc.v[j], sh.v[j]);
     }
     if (RELU) {
+      if (mask) {  // one bit per element: all the backward pass needs to know about z
+        unsigned bits = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bits |= (o.v[j] > 0.f ? 1u : 0u) << j;
+        mask[i] = (unsigned char)bits;
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) o.v[j] = fmaxf(o.v[j], 0.f);
     }
@@ -210,8 +216,9 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 template <bool RELU, bool TWO>
 __global__ void __launch_bounds__(kBnThreads)
     bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
-                         const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ y,
-                         const float* __restrict__ mean, float* partial, long long M, int C, long long rows_per_blk) {
+                         const __nv_bfloat16* __restrict__ z, const unsigned char* __restrict__ mask,
+                         const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, float* partial,
+                         long long M, int C, long long rows_per_blk) {
   extern __shared__ float smem[];
   const int C8 = C >> 3, RP = kBnThreads / C8;
   const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
@@ -232,9 +239,15 @@ __global__ void __launch_bounds__(kBnThreads)
         for (int j = 0; j < 8; ++j) g.v[j] += g2.v[j];
       }
       if (RELU) {
-        Vec8 zz = load_bf16x8(z + off);
+        if (mask) {
+          const unsigned bits = mask[off >> 3];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+          for (int j = 0; j < 8; ++j) g.v[j] = ((bits >> j) & 1u) ? g.v[j] : 0.f;
+        } else {
+          Vec8 zz = load_bf16x8(z + off);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+        }
       }
       Vec8 yy = load_bf16x8(y + off);
 #pragma unroll
@@ -299,8 +312,9 @@ __global__ void __launch_bounds__(kFinThreads)
 template <bool RELU, bool TWO, bool DRES>
 __global__ void __launch_bounds__(256)
     bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
-                        const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ y,
-                        const float* __restrict__ coef, __nv_bfloat16* __restrict__ dy,
+                        const __nv_bfloat16* __restrict__ z, const unsigned char* __restrict__ mask,
+                        const __nv_bfloat16* __restrict__ y, const float* __restrict__ coef,
+                        __nv_bfloat16* __restrict__ dy,
                         __nv_bfloat16* __restrict__ dres, long long nvec, int C8) {
   const int C = C8 * 8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
@@ -313,9 +327,15 @@ __global__ void __launch_bounds__(256)
       for (int j = 0; j < 8; ++j) g.v[j] += g2.v[j];
     }
     if (RELU) {
-      Vec8 zz = load_bf16x8(z + i * 8);
+      if (mask) {
+        const unsigned bits = mask[i];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+        for (int j = 0; j < 8; ++j) g.v[j] = ((bits >> j) & 1u) ? g.v[j] : 0.f;
+      } else {
+        Vec8 zz = load_bf16x8(z + i * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
+      }
     }
     if (DRES) store_bf16x8(dres + i * 8, g);
     Vec8 yy = load_bf16x8(y + i * 8);
@@ -353,7 +373,8 @@ extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartial
 
 static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }
 
-extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
+extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                               const float* gamma,
                                const float* beta, float* running_mean, float* running_var,
                                long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
                                float* invstd, float* scale_shift /*2C*/, float* partial, const b2_xgpu_ctx* xg,
@@ -373,10 +394,11 @@ extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, long lon
   const __nv_bfloat16* yy = (const __nv_bfloat16*)y;
   const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
   __nv_bfloat16* zz = (__nv_bfloat16*)z;
-  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  unsigned char* mk = (unsigned char*)relu_mask;
+  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   return cudaGetLastError();
 }
 
@@ -392,10 +414,11 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
   const __nv_bfloat16* yy = (const __nv_bfloat16*)y;
   const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
   __nv_bfloat16* zz = (__nv_bfloat16*)z;
-  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
-  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, nvec, C / 8);
+  unsigned char* mk = nullptr;
+  if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
+  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   return cudaGetLastError();
 }
 
@@ -408,8 +431,8 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
     }                                                                           \
   } while (0)
 
-extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, void* dy, void* dres,
-                         long long M, int C, const float* gamma, const float* mean, const float* invstd,
+extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
+                         void* dy, void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd,
                          float* dgamma, float* dbeta, int accumulate, int relu, float* coef /*3C*/, float* partial,
                          const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
   if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
@@ -421,7 +444,8 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
   const __nv_bfloat16 *a = (const __nv_bfloat16*)dz_a, *b = (const __nv_bfloat16*)dz_b,
                       *zz = (const __nv_bfloat16*)z, *yy = (const __nv_bfloat16*)y;
   const bool dzb = dz_b != nullptr;
-#define RED(R, T, ...) bn_bwd_reduce_kernel<R, T><<<nblk, kBnThreads, sm, st>>>(a, b, zz, yy, mean, partial, M, C, rpb)
+  const unsigned char* mk = (const unsigned char*)relu_mask;
+#define RED(R, T, ...) bn_bwd_reduce_kernel<R, T><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, M, C, rpb)
   B2_BWD_DISPATCH(RED, 0);
 #undef RED
   XgpuCtx ctx = xgpu_from_c(xg);
@@ -432,8 +456,8 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
   __nv_bfloat16 *dyp = (__nv_bfloat16*)dy, *drp = (__nv_bfloat16*)dres;
 #define APP(R, T, ...)                                                                                       \
   do {                                                                                                       \
-    if (dres) bn_bwd_apply_kernel<R, T, true><<<grid, 256, 0, st>>>(a, b, zz, yy, coef, dyp, drp, nvec, C / 8); \
-    else bn_bwd_apply_kernel<R, T, false><<<grid, 256, 0, st>>>(a, b, zz, yy, coef, dyp, drp, nvec, C / 8);     \
+    if (dres) bn_bwd_apply_kernel<R, T, true><<<grid, 256, 0, st>>>(a, b, zz, mk, yy, coef, dyp, drp, nvec, C / 8); \
+    else bn_bwd_apply_kernel<R, T, false><<<grid, 256, 0, st>>>(a, b, zz, mk, yy, coef, dyp, drp, nvec, C / 8);     \
   } while (0)
   B2_BWD_DISPATCH(APP, 0);
 #undef APP
@@ -493,6 +517,6 @@ extern "C" int b2_bn_fwd_train_noalloc(const void* y, const void* res, void* z, 
   if (e != cudaSuccess) return e;
   // Nothing in the scratch has to start at zero: the statistics kernel overwrites every partial the finalize
   // kernel reads, so whatever the previous call left behind is never observed.
-  return b2_bn_fwd_train(y, res, z, M, C, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps,
+  return b2_bn_fwd_train(y, res, z, /*relu_mask=*/nullptr, M, C, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps,
                          relu, mean, invstd, scale_shift, scratch, xg, xg_slot, stream);
 }

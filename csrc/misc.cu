@@ -252,31 +252,39 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
 
 // ------------------------------------------------------------------------------------------------ stem (7x7/2, Cin=3)
 // A[row][k], k = (kh*7+kw)*3 + c for k < 147, zero for 147 <= k < 192.  Reads the NCHW input batch directly.
+// One CTA per output row (n, oh): the 7 input rows x 3 channels it touches are staged in shared memory with
+// coalesced loads (zero-padded left/right), then every thread assembles 16-byte chunks of the im2col rows.
 template <typename T>
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ A,
                                                           int N, int H, int W, int Ho, int Wo) {
-  const long long total = (long long)N * Ho * Wo * 24;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int chunk = (int)(i % 24);
-    long long pix = i / 24;
-    const int ow = (int)(pix % Wo); pix /= Wo;
-    const int oh = (int)(pix % Ho);
-    const int n = (int)(pix / Ho);
-    float v[8];
+  extern __shared__ __nv_bfloat16 srow[];  // [7][3][W + 6]
+  const int Wp = W + 6;
+  const int n = blockIdx.x / Ho, oh = blockIdx.x - n * Ho;
+  for (int i = threadIdx.x; i < 21 * Wp; i += blockDim.x) {
+    const int rc = i / Wp, col = i - rc * Wp;
+    const int kh = rc / 3, c = rc - kh * 3;
+    const int h = oh * 2 - 3 + kh, w = col - 3;
+    float v = 0.f;
+    if (h >= 0 && h < H && w >= 0 && w < W) v = (float)x[((long long)(n * 3 + c) * H + h) * W + w];
+    srow[i] = __float2bfloat16(v);
+  }
+  __syncthreads();
+  __nv_bfloat16* Arow = A + (long long)blockIdx.x * Wo * 192;
+  for (int i = threadIdx.x; i < Wo * 24; i += blockDim.x) {
+    const int ow = i / 24, chunk = i - ow * 24;
+    __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int k = chunk * 8 + j;
-      float val = 0.f;
+      __nv_bfloat16 val = __float2bfloat16(0.f);
       if (k < 147) {
         const int tap = k / 3, c = k - tap * 3;
         const int kh = tap / 7, kw = tap - kh * 7;
-        const int h = oh * 2 - 3 + kh, w = ow * 2 - 3 + kw;
-        if (h >= 0 && h < H && w >= 0 && w < W) val = (float)x[((long long)(n * 3 + c) * H + h) * W + w];
+        val = srow[(kh * 3 + c) * Wp + ow * 2 + kw];
       }
       v[j] = val;
     }
-    *reinterpret_cast<uint4*>(A + i * 8) = pack8(v);
+    *reinterpret_cast<uint4*>(Arow + (long long)i * 8) = *reinterpret_cast<const uint4*>(v);
   }
 }
 // fp32 OHWI [64][147] -> bf16 [64][192] zero padded
@@ -388,11 +396,13 @@ extern "C" int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* 
 }
 extern "C" int b2_stem_im2col(const void* x, int x_is_bf16, void* A, int N, int H, int W, void* stream) {
   const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
-  const int grid = sgrid((long long)N * Ho * Wo * 24);
+  const int grid = N * Ho;
+  const size_t sm = (size_t)21 * (W + 6) * sizeof(bf16);
+  if (sm > 48 * 1024) return cudaErrorInvalidValue;  // W <= 1160
   if (x_is_bf16)
-    stem_im2col_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)A, N, H, W, Ho, Wo);
+    stem_im2col_kernel<bf16><<<grid, 256, sm, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)A, N, H, W, Ho, Wo);
   else
-    stem_im2col_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, (bf16*)A, N, H, W, Ho, Wo);
+    stem_im2col_kernel<float><<<grid, 256, sm, (cudaStream_t)stream>>>((const float*)x, (bf16*)A, N, H, W, Ho, Wo);
   return cudaGetLastError();
 }
 extern "C" int b2_stem_pack_w(const float* w, void* wp, int Cout, void* stream) {

@@ -60,8 +60,10 @@ void b2_conv_set_impl(int impl);
  * y: conv output [M,C]; z: block output; partial: scratch of b2_bn_partial_floats(C) floats.
  * ---------------------------------------------------------------------------------------------- */
 long long b2_bn_partial_floats(int C);
-int b2_bn_fwd_train(const void* y, const void* res, void* z, long long M, int C, const float* gamma,
-                    const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+/* relu_mask (optional, u8 [M*C/8]): one bit per output element, set where the ReLU passed; the backward pass can
+ * then be given the mask instead of z (16x fewer bytes). */
+int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                    const float* gamma, const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
                     float momentum, float eps, int relu, float* mean, float* invstd, float* scale_shift,
                     float* partial, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma, const float* beta,
@@ -86,8 +88,8 @@ int b2_bn_fwd_train_noalloc(const void* y, const void* res, void* z, long long M
                             long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
                             float* invstd, float* scale_shift, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 /* dz' = (dz_a + dz_b) * relu_mask(z); dy = BN backward of dz'; dres (optional) receives dz'. */
-int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* y, void* dy, void* dres, long long M,
-              int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y, void* dy,
+              void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
               int accumulate, int relu, float* coef, float* partial, const b2_xgpu_ctx* xg, int xg_slot,
               void* stream);
 

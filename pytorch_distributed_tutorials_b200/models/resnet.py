@@ -190,10 +190,10 @@ class _BnState:
 
 
 class _Rec:
-    __slots__ = ("x", "y", "z", "conv", "bn", "relu", "stem_a")
+    __slots__ = ("x", "y", "mask", "conv", "bn", "relu", "stem_a")
 
-    def __init__(self, x, y, z, conv, bn, relu, stem_a=None):
-        self.x, self.y, self.z, self.conv, self.bn, self.relu, self.stem_a = x, y, z, conv, bn, relu, stem_a
+    def __init__(self, x, y, mask, conv, bn, relu, stem_a=None):
+        self.x, self.y, self.mask, self.conv, self.bn, self.relu, self.stem_a = x, y, mask, conv, bn, relu, stem_a
 
 
 class ResNetEngine:
@@ -247,12 +247,18 @@ class ResNetEngine:
 
     def _unit(self, x, conv, bn, relu, res, training, tape):
         y = self._conv(x, conv)
-        z = self._bn_apply(y, bn, relu, res, training)
+        mask = self._new_mask(y) if (tape is not None and relu) else None
+        z = self._bn_apply(y, bn, relu, res, training, mask)
         if tape is not None:
-            tape.append(_Rec(x, y, z, conv, bn, relu))
+            tape.append(_Rec(x, y, mask, conv, bn, relu))
         return z
 
-    def _bn_apply(self, y, bn, relu, res, training):
+    @staticmethod
+    def _new_mask(y):
+        """ReLU bit mask (1 bit / element): what backward needs instead of re-reading the bf16 output."""
+        return torch.empty(y.numel() // 8, dtype=torch.uint8, device=y.device)
+
+    def _bn_apply(self, y, bn, relu, res, training, mask=None):
         st = self._bn(bn)
         use_batch_stats = training or bn.running_mean is None
         if use_batch_stats:
@@ -261,7 +267,7 @@ class ResNetEngine:
             return native.bn_fwd_train(y, res, bn.weight, bn.bias, bn.running_mean if track else None,
                                        bn.running_var if track else None,
                                        bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
-                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot)
+                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot, mask)
         return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
                                   st.scale_shift)
 
@@ -276,9 +282,10 @@ class ResNetEngine:
         y2d = convops.gemm_nt(a, self.stem_wp)
         n = x.shape[0]
         y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
-        z = self._bn_apply(y, m.bn1, True, None, training)
+        mask = self._new_mask(y) if tape is not None else None
+        z = self._bn_apply(y, m.bn1, True, None, training, mask)
         if tape is not None:
-            tape.append(_Rec(None, y, z, m.conv1, m.bn1, True, stem_a=a))
+            tape.append(_Rec(None, y, mask, m.conv1, m.bn1, True, stem_a=a))
         return z
 
     def _run_forward(self, x, training, tape):
@@ -330,9 +337,9 @@ class ResNetEngine:
         # BN backward needs dgamma/dbeta destinations up front (the finalize kernel writes them).
         dg_slot = self._slot(bn.weight)
         db_slot = self._slot(bn.bias)
-        dy, dres = native.bn_bwd(dz_a, dz_b, rec.z if rec.relu else None, rec.y, bn.weight, st.mean, st.invstd,
+        dy, dres = native.bn_bwd(dz_a, dz_b, None, rec.y, bn.weight, st.mean, st.invstd,
                                  dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
-                                 self._sync_bn_ctx(bn), self.xg_slot)
+                                 self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight

@@ -46,11 +46,12 @@ def _mc(t):
 
 # ------------------------------------------------------------------------------------------------ batch norm
 def bn_fwd_train(y, res, gamma, beta, running_mean, running_var, nbt, momentum, eps, relu, mean, invstd,
-                 scale_shift, xg=None, xg_slot=0):
-    """aten::native_batch_norm (training) + relu_ + add_ fused. Returns z."""
+                 scale_shift, xg=None, xg_slot=0, mask=None):
+    """aten::native_batch_norm (training) + relu_ + add_ fused. Returns z. ``mask`` (uint8 [M*C/8], optional)
+    receives one bit per element where the ReLU passed."""
     M, C = _mc(y)
     z = torch.empty_like(y)
-    e = _lib.lib().b2_bn_fwd_train(ptr(y), ptr(res), ptr(z), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
+    e = _lib.lib().b2_bn_fwd_train(ptr(y), ptr(res), ptr(z), ptr(mask), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
                                    ptr(running_var), ptr(nbt), c_f(momentum), c_f(eps), int(relu), ptr(mean),
                                    ptr(invstd), ptr(scale_shift), ptr(bn_partial(y.device)), _xg(xg), xg_slot,
                                    stream_ptr())
@@ -70,13 +71,13 @@ def bn_fwd_eval(y, res, gamma, beta, running_mean, running_var, eps, relu, scale
 
 
 def bn_bwd(dz_a, dz_b, z, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, want_dres, xg=None,
-           xg_slot=0):
+           xg_slot=0, mask=None):
     """aten::native_batch_norm_backward + threshold_backward + the gradient fan-in add, fused.
     Returns (dy, dres) where dres (optional) is the masked incoming gradient for the residual branch."""
     M, C = _mc(y)
     dy = torch.empty_like(y)
     dres = torch.empty_like(y) if want_dres else None
-    e = _lib.lib().b2_bn_bwd(ptr(dz_a), ptr(dz_b), ptr(z), ptr(y), ptr(dy), ptr(dres), c_ll(M), C, ptr(gamma),
+    e = _lib.lib().b2_bn_bwd(ptr(dz_a), ptr(dz_b), ptr(z), ptr(mask), ptr(y), ptr(dy), ptr(dres), c_ll(M), C, ptr(gamma),
                              ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta), int(accumulate), int(relu), ptr(coef),
                              ptr(bn_partial(y.device)), _xg(xg), xg_slot, stream_ptr())
     check(e, "b2_bn_bwd")

@@ -79,7 +79,8 @@ def test_bn_forward_backward(C, H, N, relu, res):
     rm0, rv0 = rm.clone(), rv.clone()
     mean, invstd = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
     ss, coef = torch.empty(2 * C, device=DEV), torch.empty(3 * C, device=DEV)
-    z = native.bn_fwd_train(y, r, gamma, beta, rm, rv, nbt, 0.1, 1e-5, relu, mean, invstd, ss)
+    mask = torch.zeros(y.numel() // 8, dtype=torch.uint8, device=DEV)
+    z = native.bn_fwd_train(y, r, gamma, beta, rm, rv, nbt, 0.1, 1e-5, relu, mean, invstd, ss, mask=mask)
     # reference (fp32 math on the same bf16 inputs)
     yf = y.float().requires_grad_(True)
     g32, b32 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
@@ -107,6 +108,10 @@ def test_bn_forward_backward(C, H, N, relu, res):
     assert _rel(dy, yf.grad) < 2e-2
     assert _rel(dgamma, g32.grad) < 1e-2 and _rel(dbeta, b32.grad) < 1e-2
     assert _rel(dres, up) < 1e-2
+    if relu:  # same result when the kernel is given the 1-bit mask instead of z
+        dg2, db2 = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+        dy2, dres2 = native.bn_bwd(dza, dzb, None, y, gamma, mean, invstd, dg2, db2, False, relu, coef, True, mask=mask)
+        assert torch.equal(dy2, dy) and torch.equal(dres2, dres) and torch.equal(dg2, dgamma)
 
 
 def test_bn_eval():

@@ -31,8 +31,9 @@ def _run(fn_name, y, res, gamma, beta, relu, partial):
     ss = torch.empty(2 * c, device=DEV)
     p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)  # noqa: E731
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    common = [p(y), p(res), p(z), ctypes.c_longlong(M), ctypes.c_int(c), p(gamma), p(beta), p(rm), p(rv), p(nbt),
-              ctypes.c_float(0.1), ctypes.c_float(1e-5), ctypes.c_int(int(relu)), p(mean), p(invstd), p(ss)]
+    common = [p(y), p(res), p(z)] + ([ctypes.c_void_p(0)] if partial is not None else []) + [
+        ctypes.c_longlong(M), ctypes.c_int(c), p(gamma), p(beta), p(rm), p(rv), p(nbt),
+        ctypes.c_float(0.1), ctypes.c_float(1e-5), ctypes.c_int(int(relu)), p(mean), p(invstd), p(ss)]
     if partial is not None:
         common.append(p(partial))
     err = getattr(L, fn_name)(*common, ctypes.c_void_p(0), ctypes.c_int(0), stream)
