@@ -54,6 +54,38 @@ B2_DEVICE void sgd_apply4(const SgdArgs& a, long long vi, float4 g) {
   }
 }
 
+constexpr int kUnroll = 4;  // independent 16-byte peer loads in flight per thread and peer (NVLink latency ~2 us)
+
+// Reduce U vectors (vi, vi+stride, ...) over W ranks: issue every load first, then add in rank order.
+// W is a compile-time bound on the world size (2, 4, 8) so the staging registers are sized exactly.
+template <int W, int U>
+B2_DEVICE void reduce_peers_u(const XgpuCtx& xg, long long off_f, long long vi, long long stride, long long vend,
+                              float scale, float4 (&out)[U]) {
+  float4 v[W][U];
+#pragma unroll
+  for (int r = 0; r < W; ++r) {
+    if (r < xg.world) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = vi + u * stride;
+        v[r][u] = (i < vend) ? ld_peer_f4(xg.data[r] + off_f + i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < W; ++r) {
+      if (r < xg.world) {
+        acc.x += v[r][u].x; acc.y += v[r][u].y; acc.z += v[r][u].z; acc.w += v[r][u].w;
+      }
+    }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    out[u] = acc;
+  }
+}
+
 B2_DEVICE float4 reduce_peers(const XgpuCtx& xg, long long off_f, long long vi, float scale) {
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -94,8 +126,10 @@ __global__ void __launch_bounds__(kArThreads)
 }
 
 // ------------------------------------------------------------------------------------------------ two-shot
+template <int W>
 __global__ void __launch_bounds__(kArThreads)
     allreduce_twoshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd, int write_grad) {
+  constexpr int U = (W <= 4) ? 4 : 2;  // peer loads in flight per thread: W*U vectors
   const long long slice = (nvec + xg.world - 1) / xg.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -104,7 +138,13 @@ __global__ void __launch_bounds__(kArThreads)
   xgpu_barrier(xg, blockIdx.x);
   {  // reduce-scatter: this rank owns [s0, s1)
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
-    for (long long vi = s0 + t0; vi < s1; vi += stride) st_f4(mine + vi * 4, reduce_peers(xg, off_f, vi, scale));
+    for (long long vi = s0 + t0; vi < s1; vi += stride * U) {
+      float4 r[U];
+      reduce_peers_u<W, U>(xg, off_f, vi, stride, s1, scale, r);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (vi + u * stride < s1) st_f4(mine + (vi + u * stride) * 4, r[u]);
+    }
   }
   xgpu_barrier(xg, blockIdx.x);
   // all-gather (+ update): pull every owner's reduced slice; own slice is already local
@@ -112,10 +152,19 @@ __global__ void __launch_bounds__(kArThreads)
     const int owner = (xg.rank + q) % xg.world;  // start with the local slice, then stagger peers
     const long long s0 = slice * owner, s1 = min(nvec, s0 + slice);
     const float* src = xg.data[owner] + off_f;
-    for (long long vi = s0 + t0; vi < s1; vi += stride) {
-      const float4 g = ld_peer_f4(src + vi * 4);
-      if (sgd.p32) sgd_apply4(sgd, vi, g);
-      if (write_grad && owner != xg.rank) st_f4(mine + vi * 4, g);
+    for (long long vi = s0 + t0; vi < s1; vi += stride * kUnroll) {
+      float4 g[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (vi + u * stride < s1) g[u] = ld_peer_f4(src + (vi + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = vi + u * stride;
+        if (i < s1) {
+          if (sgd.p32) sgd_apply4(sgd, i, g[u]);
+          if (write_grad && owner != xg.rank) st_f4(mine + i * 4, g[u]);
+        }
+      }
     }
   }
   xgpu_barrier(xg, blockIdx.x);  // peers are done reading this rank's slice before it is overwritten again
@@ -147,15 +196,29 @@ __global__ void __launch_bounds__(kArThreads)
   xgpu_barrier(xg, blockIdx.x);
   {
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
-    for (long long vi = s0 + t0; vi < s1; vi += stride) {
-      float4 g = multimem_ld_reduce_f4(mc + vi * 4);
-      g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
-      multimem_st_f4(mc + vi * 4, g);  // lands in every rank's buffer
+    for (long long vi = s0 + t0; vi < s1; vi += stride * kUnroll) {
+      float4 g[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (vi + u * stride < s1) g[u] = multimem_ld_reduce_f4(mc + (vi + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (vi + u * stride < s1) {
+          g[u].x *= scale; g[u].y *= scale; g[u].z *= scale; g[u].w *= scale;
+          multimem_st_f4(mc + (vi + u * stride) * 4, g[u]);  // lands in every rank's buffer
+        }
+      }
     }
   }
   xgpu_barrier(xg, blockIdx.x);
   if (sgd.p32) {
-    for (long long vi = t0; vi < nvec; vi += stride) sgd_apply4(sgd, vi, ld_peer_f4(mine + vi * 4));
+    for (long long vi = t0; vi < nvec; vi += stride) {
+      // local copy, filled by the multicast stores of every rank; read through L2 (never cached in this SM's L1)
+      const uint4 u = ld_cg_v4(mine + vi * 4);
+      const float4 g = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z),
+                                   __uint_as_float(u.w));
+      sgd_apply4(sgd, vi, g);
+    }
   }
 }
 
@@ -168,8 +231,15 @@ __global__ void __launch_bounds__(kArThreads)
     uint4* d = dst_override ? dst_override
                             : reinterpret_cast<uint4*>(reinterpret_cast<char*>(xg.data[xg.rank]) + off_bytes);
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec16; i += stride)
-      st_v4(d + i, ld_volatile_v4(s + i));
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec16; i += stride * kUnroll) {
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (i + u * stride < nvec16) v[u] = ld_volatile_v4(s + i + u * stride);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (i + u * stride < nvec16) st_v4(d + i + u * stride, v[u]);
+    }
   }
   xgpu_barrier(xg, blockIdx.x);
 }
@@ -206,7 +276,9 @@ extern "C" int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long off
   if (algo == B2_AR_AUTO) {
     // One-shot moves (W-1)*S inbound per GPU but has two barriers and no second pass: wins only when small.
     algo = (n * 4 <= (512 << 10)) ? B2_AR_ONESHOT : B2_AR_TWOSHOT;
-    if (mc_base && n * 4 >= (1 << 20)) algo = B2_AR_MULTIMEM;
+    // In-switch reduction pays off once several peers would otherwise be read one by one; with two ranks the
+    // plain peer read moves the same bytes without the extra local pass (measured, tools/comm_bench.py).
+    if (mc_base && xg.world > 2 && n * 4 >= (1 << 20)) algo = B2_AR_MULTIMEM;
   }
   if (algo == B2_AR_ONESHOT) {
     int nb = nblocks > 0 ? nblocks : B2_XGPU_CHANNELS;
@@ -230,8 +302,10 @@ extern "C" int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long off
         xg, (float*)mc_base, off_f, nvec, scale, sgd);
     return cudaGetLastError();
   }
-  allreduce_twoshot_kernel<<<clamp_blocks(nblocks, nvec / xg.world + 1), kArThreads, 0, st>>>(xg, off_f, nvec, scale,
-                                                                                             sgd, write_grad);
+  const int nb = clamp_blocks(nblocks, nvec / xg.world + 1);
+  if (xg.world <= 2) allreduce_twoshot_kernel<2><<<nb, kArThreads, 0, st>>>(xg, off_f, nvec, scale, sgd, write_grad);
+  else if (xg.world <= 4) allreduce_twoshot_kernel<4><<<nb, kArThreads, 0, st>>>(xg, off_f, nvec, scale, sgd, write_grad);
+  else allreduce_twoshot_kernel<8><<<nb, kArThreads, 0, st>>>(xg, off_f, nvec, scale, sgd, write_grad);
   return cudaGetLastError();
 }
 

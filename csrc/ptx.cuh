@@ -234,6 +234,14 @@ B2_DEVICE uint4 ld_volatile_v4(const void* p) {  // coherent (not .nc): data ano
                : "memory");
   return r;
 }
+B2_DEVICE uint4 ld_cg_v4(const void* p) {  // cache at L2 only
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 B2_DEVICE void st_v4(void* p, uint4 v) {
   asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");

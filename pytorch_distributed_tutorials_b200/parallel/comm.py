@@ -101,7 +101,7 @@ class P2PComm(_Base):
         self.window_bytes = int(window_bytes)
         self.window = SymmetricWindow(self.window_bytes, self.device, group)
         self.algo = ALGOS[algo or os.environ.get("B200DDP_ALGO", "auto")]
-        self.nblocks = int(nblocks or os.environ.get("B200DDP_COMM_BLOCKS", "48"))
+        self.nblocks = int(nblocks or os.environ.get("B200DDP_COMM_BLOCKS", "64"))
         lo, hi = torch.cuda.Stream.priority_range()
         self.stream = torch.cuda.Stream(device=self.device, priority=hi)
         self._grad_region = None
