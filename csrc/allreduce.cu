@@ -212,12 +212,18 @@ __global__ void __launch_bounds__(kArThreads)
   }
   xgpu_barrier(xg, blockIdx.x);
   if (sgd.p32) {
-    for (long long vi = t0; vi < nvec; vi += stride) {
-      // local copy, filled by the multicast stores of every rank; read through L2 (never cached in this SM's L1)
-      const uint4 u = ld_cg_v4(mine + vi * 4);
-      const float4 g = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z),
-                                   __uint_as_float(u.w));
-      sgd_apply4(sgd, vi, g);
+    // local copy, filled by the multicast stores of every rank; read through L2 (never cached in this SM's L1)
+    for (long long vi = t0; vi < nvec; vi += stride * kUnroll) {
+      uint4 u[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k)
+        if (vi + k * stride < nvec) u[k] = ld_cg_v4(mine + (vi + k * stride) * 4);
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k)
+        if (vi + k * stride < nvec)
+          sgd_apply4(sgd, vi + k * stride,
+                     make_float4(__uint_as_float(u[k].x), __uint_as_float(u[k].y), __uint_as_float(u[k].z),
+                                 __uint_as_float(u[k].w)));
     }
   }
 }
@@ -278,7 +284,7 @@ extern "C" int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long off
     algo = (n * 4 <= (512 << 10)) ? B2_AR_ONESHOT : B2_AR_TWOSHOT;
     // In-switch reduction pays off once several peers would otherwise be read one by one; with two ranks the
     // plain peer read moves the same bytes without the extra local pass (measured, tools/comm_bench.py).
-    if (mc_base && xg.world > 2 && n * 4 >= (1 << 20)) algo = B2_AR_MULTIMEM;
+    if (mc_base && xg.world > 2 && n * 4 >= (32 << 10)) algo = B2_AR_MULTIMEM;
   }
   if (algo == B2_AR_ONESHOT) {
     int nb = nblocks > 0 ? nblocks : B2_XGPU_CHANNELS;
