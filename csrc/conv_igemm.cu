@@ -452,7 +452,8 @@ template <int BN>
 struct Cfg2 {
   static constexpr int kStageBytes = BM * 128 + BN * 128;
   static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-  static constexpr int kSmem = kStages * kStageBytes + 1024 + 256;
+  static constexpr int kEpiBytes = 2 * BM * 128;  // two 128-row x 64-column bf16 panels for the TMA-store epilogue
+  static constexpr int kSmem = kStages * kStageBytes + kEpiBytes + 1024 + 256;
 };
 
 struct Item {
@@ -479,12 +480,13 @@ B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn) {
 template <int KIND, int AMODE, int BN>
 __global__ void __launch_bounds__(kThreads2, 1)
     igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const ConvParams p, int num_items) {
+                  const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
   using C = Cfg2<BN>;
   constexpr bool IM2COL = (AMODE == ACT_IM2COL);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* epi_smem = smem + C::kStages * C::kStageBytes;  // 1024-aligned: stage sizes are multiples of 1 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + C::kEpiBytes);
   uint64_t* full = bars;
   uint64_t* empty = bars + C::kStages;
   uint64_t* tfull = bars + 2 * C::kStages;       // [2] accumulator stage ready for the epilogue
@@ -618,7 +620,9 @@ __global__ void __launch_bounds__(kThreads2, 1)
     // ===================================================== epilogue warps 2..5 (TMEM lane quadrant = warp % 4)
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
-    uint32_t t = 0;
+    const bool store_thread = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
+    const bool tma_epi = (KIND != WGRAD) && p.cls == 1;
+    uint32_t t = 0, panel_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
       const Item it = decode_item(p, item, KIND, BN);
       const uint32_t acc = t & 1;
@@ -627,7 +631,46 @@ __global__ void __launch_bounds__(kThreads2, 1)
       const uint32_t taddr = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
       const int m = it.m0 + row;
       const bool ok = m < p.M;
-      if (KIND != WGRAD) {
+      if (KIND != WGRAD && tma_epi) {
+        // TMEM -> registers -> bf16 -> 128B-swizzled shared panel -> TMA store (full-line writes; the store clips
+        // rows >= M and columns >= Ncols). Panels are double buffered.
+#pragma unroll 1
+        for (int pn = 0; pn < BN / 64; ++pn, ++panel_seq) {
+          if (it.n0 + pn * 64 >= p.Ncols) break;
+          uint8_t* buf = epi_smem + (panel_seq & 1) * (BM * 128);
+          if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");  // the buffer's previous store has finished reading it
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld32(taddr + pn * 64 + h * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              if (p.bias) {
+                const int col = it.n0 + pn * 64 + h * 32 + q * 8;
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (col + e < p.Ncols)
+                    v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
+              }
+              uint4 o;
+              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              const int chunk = h * 4 + q;  // 16-byte chunk index inside the 128-byte panel row
+              *reinterpret_cast<uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+            }
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (store_thread) {
+            tma_store_2d(buf, &tmC, it.n0 + pn * 64, it.m0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+      } else if (KIND != WGRAD) {
         long long orow_idx = m;
         if (KIND == DGRAD && p.cls > 1 && ok) {
           int n, i, j;
@@ -681,6 +724,7 @@ __global__ void __launch_bounds__(kThreads2, 1)
     }
   }
 
+  if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores have landed
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_free<2 * BN>(tmem_base);
@@ -700,6 +744,11 @@ static int num_sms() {
 template <int KIND, int AMODE, int BN>
 static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int items,
                            cudaStream_t st) {
+  CUtensorMap tmC = tmB;  // wgrad and class-strided dgrad never dereference it
+  if (KIND != WGRAD && p.cls == 1) {
+    int e = make_tmap_2d_bf16(&tmC, p.out, (uint64_t)p.Ncols, (uint64_t)p.M, 64, 128);
+    if (e) return (cudaError_t)e;
+  }
   auto kern = igemm2_kernel<KIND, AMODE, BN>;
   static bool configured = false;
   if (!configured) {
@@ -708,7 +757,7 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     configured = true;
   }
   const int grid = items < num_sms() ? items : num_sms();
-  kern<<<grid, kThreads2, Cfg2<BN>::kSmem, st>>>(tmA, tmB, p, items);
+  kern<<<grid, kThreads2, Cfg2<BN>::kSmem, st>>>(tmA, tmB, tmC, p, items);
   return cudaGetLastError();
 }
 template <int KIND, int AMODE>

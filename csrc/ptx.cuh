@@ -92,6 +92,14 @@ B2_DEVICE void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, 
       : "memory");
 }
 
+// TMA store of a shared-memory box to a 2-D tensor (bulk async group completion; out-of-bounds parts are clipped).
+B2_DEVICE void tma_store_2d(const void* smem_src, const CUtensorMap* m, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+
 // TMA im2col load (NHWC): `pixelsPerColumn` consecutive output positions starting at base pixel (w,h,n), channels
 // [c, c+channelsPerPixel), each displaced by the filter-tap offset (off_w, off_h); padding reads as zero.
 B2_DEVICE void tma_load_im2col(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
