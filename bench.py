@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--bucket-cap-mb", type=float, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fuse-optimizer", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying "
+                    "the captured whole-step CUDA graph")
     ap.add_argument("--reference-strict", action="store_true",
                     help="report the reference as unavailable instead of running the minimally-fixed harness")
     return ap.parse_args()
@@ -130,14 +132,11 @@ def build_ours(args, local_rank, world):
                     fuse_with_backward=not args.no_fuse_optimizer)
     crit = CrossEntropyLoss()
     ddp.train()
-
-    def step(x, y):
-        opt.zero_grad()
-        loss = crit(ddp(x), y)
-        loss.backward()
-        opt.step()
-        return loss
-
+    from pytorch_distributed_tutorials_b200.utils.graph import GraphedTrainStep
+    # public API for a whole training step: zero_grad -> forward -> loss -> backward (+ bucketed all-reduce with
+    # the fused SGD epilogue) -> step, captured into one CUDA graph after three eager steps
+    step = GraphedTrainStep(ddp, crit, opt, warmup=3, enabled=not args.no_graph)
+    ddp._bench_step = step
     return step, ddp
 
 
@@ -307,7 +306,8 @@ def main():
                        "sync_bn": bool(args.sync_bn),
                        "l2": "per-step inputs (%.0f MB/GPU) exceed the 126 MB L2; no explicit flush" %
                              (args.batch * 3 * args.image_size ** 2 * 4 / 1e6),
-                       "backend": getattr(ddp, "backend", "torch-ddp/nccl" if world > 1 else "none")},
+                       "backend": getattr(ddp, "backend", "torch-ddp/nccl" if world > 1 else "none"),
+                       "cuda_graph": bool(getattr(getattr(ddp, "_bench_step", None), "captures", 0))},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "ours" else 0,
             "exposed_comm_ms_per_step": exposed,
         }

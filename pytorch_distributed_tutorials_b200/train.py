@@ -75,6 +75,8 @@ def build_parser():
     p.add_argument("--max-steps", type=int, default=0, help="stop after this many optimizer steps (0 = no limit)")
     p.add_argument("--reshuffle-each-epoch", action="store_true", help="call sampler.set_epoch (the reference never does)")
     p.add_argument("--log-every", type=int, default=0, help="print loss / images-per-second every N steps")
+    p.add_argument("--cuda-graph", action="store_true",
+                   help="capture the whole training step into a CUDA graph (one launch per step)")
     return p
 
 
@@ -112,6 +114,11 @@ def main(argv=None):
     optimizer = optim.SGD(ddp_model.parameters(), lr=args.learning_rate, momentum=0.9, weight_decay=1e-5,
                           fuse_with_backward=use_cuda and not args.no_fuse_optimizer)
 
+    graphed = None
+    if args.cuda_graph and use_cuda:
+        from .utils.graph import GraphedTrainStep
+        graphed = GraphedTrainStep(ddp_model, criterion, optimizer)
+
     steps = 0
     for epoch in range(args.num_epochs):
         print("Local Rank: {}, Epoch: {}, Training ...".format(local_rank, epoch), flush=True)
@@ -129,11 +136,14 @@ def main(argv=None):
         t0, seen = time.perf_counter(), 0
         for data in batches:
             inputs, labels = data[0].to(device), data[1].to(device)
-            optimizer.zero_grad()
-            outputs = ddp_model(inputs)
-            loss = criterion(outputs, labels)
-            loss.backward()
-            optimizer.step()
+            if graphed is not None:
+                loss = graphed(inputs, labels)
+            else:
+                optimizer.zero_grad()
+                outputs = ddp_model(inputs)
+                loss = criterion(outputs, labels)
+                loss.backward()
+                optimizer.step()
             steps += 1
             seen += inputs.shape[0]
             if args.log_every and steps % args.log_every == 0:

@@ -69,7 +69,9 @@ class DevicePrefetcher:
         with torch.cuda.stream(self.stream):
             xd = x.to(self.device, non_blocking=True)
             yd = y.to(self.device, non_blocking=True)
-        return xd, yd, (x, y)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)      # this batch's copies only: later copies must not hold the consumer back
+        return xd, yd, ev, (x, y)
 
     def __iter__(self):
         it = iter(self.loader)
@@ -84,7 +86,7 @@ class DevicePrefetcher:
             except StopIteration:
                 nxt = None
             if self.stream is not None:
-                torch.cuda.current_stream(self.device).wait_stream(self.stream)
+                torch.cuda.current_stream(self.device).wait_event(cur[2])
                 cur[0].record_stream(torch.cuda.current_stream(self.device))
                 cur[1].record_stream(torch.cuda.current_stream(self.device))
             yield cur[0], cur[1]
