@@ -350,9 +350,11 @@ class ResNetEngine:
             grads[id(w)] = g
             return None, dres
         s, pd = conv.stride[0], conv.padding[0]
+        # dgrad first: delivering the weight gradient may complete a bucket, and the fused all-reduce + SGD kernel
+        # that this triggers rewrites the bucket's weights — every reader of the old weights must already be queued
+        dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd) if need_dx else None
         g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
         grads[id(w)] = g
-        dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd) if need_dx else None
         return dx, dres
 
     def _slot(self, p):
@@ -378,9 +380,9 @@ class ResNetEngine:
         dl = dlogits if dlogits.dtype == torch.bfloat16 else dlogits.to(torch.bfloat16)
         dl = dl.contiguous()
         # classifier: bias grad (column sum), weight grad (dl^T @ pooled), input grad (dl @ W)
+        dpooled = convops.gemm_nn(dl, self._w16(m.fc.weight))   # before the fc gradients are delivered (see _unit_bwd)
         grads[id(m.fc.bias)] = self._deliver(m.fc.bias, lambda out, acc: native.colsum_bf16(dl, out, acc))
         grads[id(m.fc.weight)] = self._deliver(m.fc.weight, lambda out, acc: convops.gemm_tn(dl, pooled, out, acc))
-        dpooled = convops.gemm_nn(dl, self._w16(m.fc.weight))
         da, db = native.avgpool_bwd(dpooled, feat_shape), None
         for blk, bt in reversed(block_tapes):
             n_main = len(blk.units())

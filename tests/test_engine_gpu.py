@@ -164,3 +164,29 @@ def test_graphed_train_step_matches_eager():
     assert nbt_g == nbt_e == 8
     assert all(abs(a - b) <= 1e-5 * max(1.0, abs(b)) for a, b in zip(l_g, l_e)), (l_g, l_e)
     assert all(torch.equal(a, b) for a, b in zip(p_g, p_e))       # deterministic kernels: bit-identical weights
+
+
+def test_fused_reduce_update_equals_update_in_step():
+    """Applying SGD as the epilogue of each bucket's reduction (during backward) must give exactly the weights that
+    running the same update inside optimizer.step() gives: no kernel may read a weight after its bucket was updated."""
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    torch.manual_seed(4)
+    base = resnet50().to(DEV)
+    twin = copy.deepcopy(base)
+    x = torch.randn(8, 3, 64, 64, device=DEV)
+    y = torch.randint(0, 1000, (8,), device=DEV)
+    results = []
+    for net, fuse in ((base, True), (twin, False)):
+        ddp = DistributedDataParallel(net, device_ids=[0], bucket_cap_mb=4)   # many buckets
+        opt = optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4, fuse_with_backward=fuse)
+        crit = CrossEntropyLoss()
+        for _ in range(3):
+            opt.zero_grad()
+            crit(ddp(x), y).backward()
+            opt.step()
+        results.append([p.detach().clone() for p in ddp.parameters()])
+        assert len(ddp.store.buckets) > 10
+    assert all(torch.equal(a, b) for a, b in zip(*results))

@@ -210,3 +210,43 @@ def test_syncbn_in_kernel_stats_match_torch():
     for r in outs:
         for k, v in r.items():
             assert v < 3e-2, (k, v, r)
+
+
+def _graph_ddp(rank, world):
+    import copy
+    import torch.distributed as dist
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    from pytorch_distributed_tutorials_b200.utils.graph import GraphedTrainStep
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    base = resnet18().to(dev)
+    twin = copy.deepcopy(base)
+    g = torch.Generator(device=dev).manual_seed(10 + rank)
+    xs = [torch.randn(16, 3, 32, 32, device=dev, generator=g) for _ in range(2)]
+    ys = [torch.randint(0, 10, (16,), device=dev, generator=g) for _ in range(2)]
+    out = []
+    for net, graph in ((base, True), (twin, False)):
+        ddp = DistributedDataParallel(net, device_ids=[rank])
+        opt = optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
+        step = GraphedTrainStep(ddp, CrossEntropyLoss(), opt, warmup=2, enabled=graph)
+        losses = [float(step(xs[i % 2], ys[i % 2]).item()) for i in range(7)]
+        torch.cuda.synchronize()
+        dist.barrier()
+        out.append((losses, torch.cat([p.detach().reshape(-1) for p in ddp.parameters()]).clone(), step.captures))
+    (lg, pg, caps), (le, pe, _) = out
+    other = pg.clone()
+    dist.broadcast(other, 0)
+    return {"captures": caps, "same_as_eager": bool(torch.equal(pg, pe)), "ident": bool(torch.equal(pg, other)),
+            "lg": lg, "le": le}
+
+
+def test_graph_captured_step_with_p2p_allreduce_matches_eager():
+    _need(2)
+    outs = run_ranks(_graph_ddp, world=2, backend="b200", timeout=600)
+    for r in outs:
+        assert r["captures"] == 1
+        assert r["ident"], "replicas drifted apart under graph replay"
+        assert r["same_as_eager"], (r["lg"], r["le"])
