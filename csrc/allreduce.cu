@@ -250,12 +250,32 @@ __global__ void __launch_bounds__(kArThreads)
   xgpu_barrier(xg, blockIdx.x);
 }
 
+// Multicast broadcast: the source rank pushes the region through the NVSwitch multicast address, one store
+// reaches every rank's window (broadcast_mc).
+__global__ void __launch_bounds__(kArThreads)
+    broadcast_mc_kernel(XgpuCtx xg, char* mc_base, long long off_bytes, long long nvec16, int src) {
+  xgpu_barrier(xg, blockIdx.x);
+  if (xg.rank == src) {
+    const uint4* s = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(xg.data[src]) + off_bytes);
+    float* d = reinterpret_cast<float*>(mc_base + off_bytes);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec16; i += stride) {
+      const uint4 v = ld_cg_v4(s + i);
+      multimem_st_f4(d + i * 4, make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z),
+                                            __uint_as_float(v.w)));
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);
+}
+
 // Plain device-side barrier (one CTA per rank): orders everything before it on all ranks' streams.
 __global__ void barrier_kernel(XgpuCtx xg, int channel) { xgpu_barrier(xg, channel); }
 
 }  // namespace b2
 
 using namespace b2;
+
+B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_allreduce)
 
 static int clamp_blocks(int nblocks, long long nvec) {
   long long need = (nvec + kArThreads - 1) / kArThreads;
@@ -322,6 +342,16 @@ extern "C" int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long
   const long long nvec = nbytes >> 4;
   broadcast_kernel<<<clamp_blocks(nblocks, nvec), kArThreads, 0, (cudaStream_t)stream>>>(xg, offset_bytes, nvec, src,
                                                                                         (uint4*)dst_override);
+  return cudaGetLastError();
+}
+
+extern "C" int b2_broadcast_mc(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long nbytes,
+                               int src, int nblocks, void* stream) {
+  if (!ctx || !mc_base || nbytes <= 0 || (nbytes & 15) || (offset_bytes & 15)) return cudaErrorInvalidValue;
+  XgpuCtx xg = xgpu_from_c(ctx);
+  const long long nvec = nbytes >> 4;
+  broadcast_mc_kernel<<<clamp_blocks(nblocks, nvec), kArThreads, 0, (cudaStream_t)stream>>>(
+      xg, (char*)mc_base, offset_bytes, nvec, src);
   return cudaGetLastError();
 }
 

@@ -370,6 +370,8 @@ static int stream_grid(long long nvec) {
 
 using namespace b2;
 
+B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_bn)
+
 extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartialBlocks * 2 * C; }
 
 static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }

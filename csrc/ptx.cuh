@@ -15,7 +15,7 @@ namespace b2 {
 // bounded in wall time: after B2_SPIN_TIMEOUT_NS the kernel traps and the launch surfaces as a CUDA error
 // on the host (the host-side watchdog in csrc/symm.cu then turns that into a clean non-zero exit).
 #ifndef B2_SPIN_TIMEOUT_NS
-#define B2_SPIN_TIMEOUT_NS 20000000000ull  // 20 s
+#define B2_SPIN_TIMEOUT_NS 20000000000ull  // 20 s (default; b2_set_spin_timeout_ms changes it at run time)
 #endif
 
 B2_DEVICE uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -54,6 +54,15 @@ B2_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Per-translation-unit copy of the timeout (a plain __device__ variable would need relocatable device code to be
+// shared across .cu files); every file that spins exports a setter through B2_DEFINE_SPIN_TIMEOUT_SETTER.
+static __device__ unsigned long long g_spin_timeout_ns = B2_SPIN_TIMEOUT_NS;
+B2_DEVICE uint64_t spin_timeout_ns() { return g_spin_timeout_ns; }
+#define B2_DEFINE_SPIN_TIMEOUT_SETTER(name)                                                     \
+  extern "C" int name(unsigned long long ns) {                                                  \
+    return (int)cudaMemcpyToSymbol(b2::g_spin_timeout_ns, &ns, sizeof(ns), 0, cudaMemcpyHostToDevice); \
+  }
+
 B2_DEVICE uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -67,7 +76,7 @@ struct SpinGuard {
     if ((++polls & 0x3FFu) == 0) {
       const uint64_t now = global_timer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > B2_SPIN_TIMEOUT_NS) __trap();
+      else if (now - t0 > spin_timeout_ns()) __trap();
     }
   }
 };

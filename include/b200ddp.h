@@ -173,7 +173,14 @@ int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, 
                  int first_step, int write_grad, int nblocks, void* stream);
 int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbytes, int src, void* dst_override,
                  int nblocks, void* stream);
+/* Broadcast through the NVSwitch multicast mapping: only the source rank stores, the switch replicates. */
+int b2_broadcast_mc(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long nbytes, int src,
+                    int nblocks, void* stream);
 int b2_xgpu_barrier(const b2_xgpu_ctx* ctx, int channel, void* stream);
+/* Device-side waits on peers trap after this long (default 20 s). One setter per translation unit that spins;
+ * parallel/comm.py calls both. */
+int b2_set_spin_timeout_ns_allreduce(unsigned long long ns);
+int b2_set_spin_timeout_ns_bn(unsigned long long ns);
 
 #ifdef __cplusplus
 }

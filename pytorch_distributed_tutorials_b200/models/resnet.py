@@ -10,6 +10,7 @@ BN-backward(+ReLU mask, + gradient fan-in) -> dgrad / wgrad kernels, writes para
 their DDP bucket slots and tells the reducer as each one lands.  On CPU (gloo plumbing config) or with
 ``B200DDP_FORCE_TORCH=1`` the same modules run through stock PyTorch ops, which is also the numerical oracle.
 """
+import os
 from typing import List, Optional, Type, Union
 
 import torch
@@ -18,6 +19,8 @@ import torch.nn.functional as F
 
 from ..ops import _lib, conv as convops, native
 from ..parallel.flat import store_of
+
+_NVTX = os.environ.get("B200DDP_NVTX", "0") == "1"   # NVTX ranges around forward / backward for nsys / ncu
 
 
 def conv3x3(inp, out, stride=1):
@@ -405,6 +408,16 @@ class ResNetEngine:
     def __call__(self, x):
         m = self.model
         training = m.training
+        if _NVTX:
+            torch.cuda.nvtx.range_push("b200ddp.resnet.forward")
+            try:
+                return self._call(x, training)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return self._call(x, training)
+
+    def _call(self, x, training):
+        m = self.model
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.params):
             return _EngineFn.apply(self, x, training, *self.params)
         return self._run_forward(x, training, None).float()
@@ -426,7 +439,13 @@ class _EngineFn(torch.autograd.Function):
         tape, ctx.tape = ctx.tape, None
         if tape is None:
             raise RuntimeError("the native engine's activations were already consumed by a previous backward()")
-        grads = engine._run_backward(tape, dlogits)
+        if _NVTX:
+            torch.cuda.nvtx.range_push("b200ddp.resnet.backward")
+        try:
+            grads = engine._run_backward(tape, dlogits)
+        finally:
+            if _NVTX:
+                torch.cuda.nvtx.range_pop()
         out = []
         for p in engine.params:
             g = grads.get(id(p))

@@ -106,7 +106,17 @@ class P2PComm(_Base):
         self.stream = torch.cuda.Stream(device=self.device, priority=hi)
         self._grad_region = None
         self.write_grad = os.environ.get("B200DDP_WRITE_GRAD", "1") == "1"
+        self.use_mc_broadcast = os.environ.get("B200DDP_MC_BROADCAST", "1") == "1"
         self._events = []
+        t = os.environ.get("B200DDP_SPIN_TIMEOUT_MS")
+        if t:
+            self.set_spin_timeout_ms(int(t))
+
+    def set_spin_timeout_ms(self, ms):
+        """How long a kernel may wait for a peer before it traps (failure detection; default 20 s)."""
+        ns = ctypes.c_ulonglong(int(ms) * 1000000)
+        check(_lib.lib().b2_set_spin_timeout_ns_allreduce(ns), "b2_set_spin_timeout_ns_allreduce")
+        check(_lib.lib().b2_set_spin_timeout_ns_bn(ns), "b2_set_spin_timeout_ns_bn")
 
     # gradient buckets are carved out of the window so that peers can read them
     def grad_alloc(self, numel):
@@ -155,9 +165,16 @@ class P2PComm(_Base):
         st = stream or torch.cuda.current_stream(self.device)
         pad = self.PAD_COMPUTE if pad is None else pad
         nb = (nbytes + 15) // 16 * 16
-        e = _lib.lib().b2_broadcast(ctypes.byref(self.window.ctx(pad)), c_ll(offset), c_ll(nb), src, c_p(0),
-                                    min(self.nblocks, 16 if nb < (1 << 20) else 64), c_p(st.cuda_stream))
-        check(e, "b2_broadcast")
+        blocks = min(self.nblocks, 16 if nb < (1 << 20) else 64)
+        if self.mc_base and self.use_mc_broadcast and self.world > 2:
+            # one multicast store per 16 bytes on the source instead of W-1 peer pulls
+            e = _lib.lib().b2_broadcast_mc(ctypes.byref(self.window.ctx(pad)), c_p(self.mc_base), c_ll(offset),
+                                           c_ll(nb), src, blocks, c_p(st.cuda_stream))
+            check(e, "b2_broadcast_mc")
+        else:
+            e = _lib.lib().b2_broadcast(ctypes.byref(self.window.ctx(pad)), c_ll(offset), c_ll(nb), src, c_p(0),
+                                        blocks, c_p(st.cuda_stream))
+            check(e, "b2_broadcast")
         _lib.count_launch()
 
     def broadcast_(self, tensors, src=0):

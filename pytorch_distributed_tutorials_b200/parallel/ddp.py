@@ -134,6 +134,8 @@ class DistributedDataParallel(nn.Module):
         self._fused_args = None
         self._in_backward_iteration = False
         self._ready_ids = set()
+        self.debug = os.environ.get("B200DDP_DEBUG", "0") == "1"
+        self._iter_log_start = 0
         self.measure_exposed = os.environ.get("B200DDP_MEASURE_EXPOSED", "1") == "1"
         self._exposed_events = []
         self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook) for p in ordered]
@@ -296,9 +298,24 @@ class DistributedDataParallel(nn.Module):
             self._watchdog_evt.record()
             _lib.lib().b2_watchdog_watch(ctypes.c_void_p(self._watchdog_evt.cuda_event))
         self.iterations += 1
+        if self.debug and self.world > 1 and not torch.cuda.is_current_stream_capturing():
+            self._check_collective_order()
         if left:
             raise RuntimeError("%d gradient bucket(s) never became ready: some parameters took no part in the "
                                "loss (find_unused_parameters is not supported)" % left)
+
+    def _check_collective_order(self):
+        """Debug mode (B200DDP_DEBUG=1): the epoch-numbered device barriers require every rank to issue the same
+        kernels in the same order; compare this iteration's collective sequence across ranks over the CPU control
+        plane and fail loudly on the first divergence instead of hanging in a spin loop."""
+        mine = [tuple(c) for c in self.comm.launch_log[self._iter_log_start:]]
+        self._iter_log_start = len(self.comm.launch_log)
+        seqs = [None] * self.world
+        dist.all_gather_object(seqs, mine, group=self.process_group)
+        for r, s in enumerate(seqs):
+            if s != seqs[0]:
+                raise RuntimeError("collective order diverged at iteration %d: rank 0 issued %s, rank %d issued %s"
+                                   % (self.iterations, seqs[0][:8], r, s[:8]))
 
     @contextlib.contextmanager
     def no_sync(self):

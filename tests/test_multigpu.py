@@ -250,3 +250,58 @@ def test_graph_captured_step_with_p2p_allreduce_matches_eager():
         assert r["captures"] == 1
         assert r["ident"], "replicas drifted apart under graph replay"
         assert r["same_as_eager"], (r["lg"], r["le"])
+
+
+def _fault(rank, world):
+    """Rank 1 dies mid-training; rank 0's next collective waits for it, the device-side spin bound trips and the
+    process must surface an error instead of hanging."""
+    import os
+    import time
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    ddp = DistributedDataParallel(resnet18().to(dev), device_ids=[rank])
+    ddp.comm.set_spin_timeout_ms(2000)
+    opt = optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9)
+    crit = CrossEntropyLoss()
+    x = torch.randn(8, 3, 32, 32, device=dev)
+    y = torch.randint(0, 10, (8,), device=dev)
+    t0 = time.time()
+    try:
+        for it in range(4):
+            if rank == 1 and it == 2:
+                torch.cuda.synchronize()
+                os._exit(0)          # simulated crash: no clean-up, no goodbye
+            opt.zero_grad()
+            crit(ddp(x), y).backward()
+            opt.step()
+            torch.cuda.synchronize()
+        return {"error": None, "seconds": time.time() - t0}
+    except Exception as e:  # noqa: BLE001
+        return {"error": type(e).__name__ + ": " + str(e)[:200], "seconds": time.time() - t0}
+
+
+def test_peer_failure_is_detected_not_hung():
+    _need(2)
+    import torch.multiprocessing as mp
+    from _dist_utils import _entry, free_port
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=_entry, args=(r, 2, port, _fault, "b200", (), q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    rank, status, out = q.get(timeout=120)       # only rank 0 reports; rank 1 has exited
+    for p in procs:
+        p.join(timeout=30)
+        if p.is_alive():
+            p.terminate()
+    assert rank == 0
+    # either our wrapper returned the CUDA error, or the harness caught it: both mean "detected, not hung"
+    msg = out["error"] if status == "ok" else out
+    assert msg is not None and ("CUDA" in msg or "launch failure" in msg or "trap" in msg.lower() or "error" in msg.lower()), out
+    if status == "ok":
+        assert out["seconds"] < 60
