@@ -268,6 +268,144 @@ __global__ void __launch_bounds__(kArThreads)
   xgpu_barrier(xg, blockIdx.x);
 }
 
+// ------------------------------------------------------------------------------------------------ bf16 wire
+// Same algorithms with the gradients travelling as bf16 (half the NVLink bytes; the counterpart of torch's
+// bf16_compress_hook): each rank first casts its fp32 bucket into a bf16 staging area of the symmetric window,
+// peers' values are accumulated in fp32, the average is rounded to bf16 once, and the SGD epilogue / the fp32
+// gradient written back use that value on every rank (so replicas stay bit-identical).
+struct Bf16x8 {
+  float v[8];
+};
+B2_DEVICE Bf16x8 unpack_bf16x8(uint4 u) {
+  Bf16x8 r;
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y; r.v[4] = c.x; r.v[5] = c.y; r.v[6] = d.x; r.v[7] = d.y;
+  return r;
+}
+B2_DEVICE uint4 pack_bf16x8(const Bf16x8& r) {
+  return make_uint4(pack_bf16x2(r.v[0], r.v[1]), pack_bf16x2(r.v[2], r.v[3]), pack_bf16x2(r.v[4], r.v[5]),
+                    pack_bf16x2(r.v[6], r.v[7]));
+}
+// vector index v8 covers elements [8*v8, 8*v8+8)
+B2_DEVICE void consume_avg8(const SgdArgs& sgd, float* g32_out, long long v8, const Bf16x8& g) {
+  if (sgd.p32) {
+    sgd_apply4(sgd, 2 * v8, make_float4(g.v[0], g.v[1], g.v[2], g.v[3]));
+    sgd_apply4(sgd, 2 * v8 + 1, make_float4(g.v[4], g.v[5], g.v[6], g.v[7]));
+  }
+  if (g32_out) {
+    st_f4(g32_out + v8 * 8, make_float4(g.v[0], g.v[1], g.v[2], g.v[3]));
+    st_f4(g32_out + v8 * 8 + 4, make_float4(g.v[4], g.v[5], g.v[6], g.v[7]));
+  }
+}
+B2_DEVICE void cast_local_to_wire(const float* __restrict__ g32, __nv_bfloat16* wire, long long nvec8,
+                                  long long t0, long long stride) {
+  for (long long v = t0; v < nvec8; v += stride) {
+    const float4 a = *reinterpret_cast<const float4*>(g32 + v * 8);
+    const float4 b = *reinterpret_cast<const float4*>(g32 + v * 8 + 4);
+    st_v4(wire + v * 8, make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y),
+                                   pack_bf16x2(b.z, b.w)));
+  }
+}
+template <int W>
+B2_DEVICE Bf16x8 reduce_wire(const XgpuCtx& xg, long long off_h, long long v8, float scale) {
+  uint4 u[W];
+#pragma unroll
+  for (int r = 0; r < W; ++r)
+    if (r < xg.world) u[r] = ld_volatile_v4(reinterpret_cast<const __nv_bfloat16*>(xg.data[r]) + off_h + v8 * 8);
+  Bf16x8 acc;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc.v[j] = 0.f;
+#pragma unroll
+  for (int r = 0; r < W; ++r) {
+    if (r < xg.world) {
+      const Bf16x8 x = unpack_bf16x8(u[r]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc.v[j] += x.v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc.v[j] *= scale;
+  return unpack_bf16x8(pack_bf16x8(acc));  // round once: every consumer sees the same bf16 value
+}
+
+template <int W>
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_oneshot_bf16_kernel(XgpuCtx xg, long long off_h, long long nvec8, float scale, const float* g32_in,
+                                  float* g32_out, SgdArgs sgd) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  cast_local_to_wire(g32_in, reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h, nvec8, t0, stride);
+  xgpu_barrier(xg, blockIdx.x);
+  for (long long v = t0; v < nvec8; v += stride) consume_avg8(sgd, g32_out, v, reduce_wire<W>(xg, off_h, v, scale));
+  xgpu_barrier(xg, blockIdx.x);  // peers are done with this rank's staging area
+}
+
+template <int W>
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_twoshot_bf16_kernel(XgpuCtx xg, long long off_h, long long nvec8, float scale, const float* g32_in,
+                                  float* g32_out, SgdArgs sgd) {
+  const long long slice = (nvec8 + xg.world - 1) / xg.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  __nv_bfloat16* mine = reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h;
+  cast_local_to_wire(g32_in, mine, nvec8, t0, stride);
+  xgpu_barrier(xg, blockIdx.x);
+  {
+    const long long s0 = slice * xg.rank, s1 = min(nvec8, s0 + slice);
+    for (long long v = s0 + t0; v < s1; v += stride) st_v4(mine + v * 8, pack_bf16x8(reduce_wire<W>(xg, off_h, v, scale)));
+  }
+  xgpu_barrier(xg, blockIdx.x);
+  for (int q = 0; q < xg.world; ++q) {
+    const int owner = (xg.rank + q) % xg.world;
+    const long long s0 = slice * owner, s1 = min(nvec8, s0 + slice);
+    const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(xg.data[owner]) + off_h;
+    for (long long v = s0 + t0; v < s1; v += stride * 2) {
+      uint4 u0 = ld_volatile_v4(src + v * 8), u1 = make_uint4(0, 0, 0, 0);
+      const bool two = (v + stride) < s1;
+      if (two) u1 = ld_volatile_v4(src + (v + stride) * 8);
+      consume_avg8(sgd, g32_out, v, unpack_bf16x8(u0));
+      if (two) consume_avg8(sgd, g32_out, v + stride, unpack_bf16x8(u1));
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);
+}
+
+B2_DEVICE uint4 multimem_ld_reduce_bf16x8(const __nv_bfloat16* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+B2_DEVICE void multimem_st_bf16x8(__nv_bfloat16* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_multimem_bf16_kernel(XgpuCtx xg, __nv_bfloat16* mc_base, long long off_h, long long nvec8, float scale,
+                                   const float* g32_in, float* g32_out, SgdArgs sgd) {
+  const long long slice = (nvec8 + xg.world - 1) / xg.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  __nv_bfloat16* mine = reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h;
+  __nv_bfloat16* mc = mc_base + off_h;
+  cast_local_to_wire(g32_in, mine, nvec8, t0, stride);
+  xgpu_barrier(xg, blockIdx.x);
+  {
+    const long long s0 = slice * xg.rank, s1 = min(nvec8, s0 + slice);
+    for (long long v = s0 + t0; v < s1; v += stride) {
+      Bf16x8 g = unpack_bf16x8(multimem_ld_reduce_bf16x8(mc + v * 8));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g.v[j] *= scale;
+      multimem_st_bf16x8(mc + v * 8, pack_bf16x8(g));
+    }
+  }
+  xgpu_barrier(xg, blockIdx.x);
+  for (long long v = t0; v < nvec8; v += stride) consume_avg8(sgd, g32_out, v, unpack_bf16x8(ld_cg_v4(mine + v * 8)));
+}
+
 // Plain device-side barrier (one CTA per rank): orders everything before it on all ranks' streams.
 __global__ void barrier_kernel(XgpuCtx xg, int channel) { xgpu_barrier(xg, channel); }
 
@@ -342,6 +480,40 @@ extern "C" int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long
   const long long nvec = nbytes >> 4;
   broadcast_kernel<<<clamp_blocks(nblocks, nvec), kArThreads, 0, (cudaStream_t)stream>>>(xg, offset_bytes, nvec, src,
                                                                                         (uint4*)dst_override);
+  return cudaGetLastError();
+}
+
+extern "C" int b2_allreduce_bf16(const b2_xgpu_ctx* ctx, void* mc_base, long long wire_offset_bytes, long long n,
+                                 int algo, float scale, const float* g32_in, float* g32_out, float* p32, float* mom,
+                                 void* shadow_bf16, float lr, float momentum, float weight_decay, int first_step,
+                                 int nblocks, void* stream) {
+  if (!ctx || n <= 0 || (n & 7) || (wire_offset_bytes & 15) || !g32_in) return cudaErrorInvalidValue;
+  XgpuCtx xg = xgpu_from_c(ctx);
+  const long long nvec8 = n >> 3;
+  const long long off_h = wire_offset_bytes >> 1;
+  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (algo == B2_AR_AUTO) {
+    algo = (n * 2 <= (256 << 10)) ? B2_AR_ONESHOT : B2_AR_TWOSHOT;
+    if (mc_base && xg.world > 2 && n * 2 >= (32 << 10)) algo = B2_AR_MULTIMEM;
+  }
+  const int nb1 = clamp_blocks(nblocks, nvec8);
+#define B2_BF16_DISPATCH(KERN, NB)                                                                          \
+  do {                                                                                                      \
+    if (xg.world <= 2) KERN<2><<<NB, kArThreads, 0, st>>>(xg, off_h, nvec8, scale, g32_in, g32_out, sgd);   \
+    else if (xg.world <= 4) KERN<4><<<NB, kArThreads, 0, st>>>(xg, off_h, nvec8, scale, g32_in, g32_out, sgd); \
+    else KERN<8><<<NB, kArThreads, 0, st>>>(xg, off_h, nvec8, scale, g32_in, g32_out, sgd);                 \
+  } while (0)
+  if (algo == B2_AR_ONESHOT) {
+    B2_BF16_DISPATCH(allreduce_oneshot_bf16_kernel, nb1);
+  } else if (algo == B2_AR_MULTIMEM) {
+    if (!mc_base) return cudaErrorInvalidValue;
+    allreduce_multimem_bf16_kernel<<<nb1, kArThreads, 0, st>>>(xg, (__nv_bfloat16*)mc_base, off_h, nvec8, scale,
+                                                               g32_in, g32_out, sgd);
+  } else {
+    B2_BF16_DISPATCH(allreduce_twoshot_bf16_kernel, nb1);
+  }
+#undef B2_BF16_DISPATCH
   return cudaGetLastError();
 }
 

@@ -173,6 +173,12 @@ int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, 
                  int first_step, int write_grad, int nblocks, void* stream);
 int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbytes, int src, void* dst_override,
                  int nblocks, void* stream);
+/* bf16 wire format (the counterpart of torch's bf16_compress_hook): the kernel casts this rank's fp32 bucket
+ * (g32_in, local) into a bf16 staging area at wire_offset_bytes of the window, reduces the peers' staging areas in
+ * fp32, rounds the average to bf16 once, and feeds the SGD epilogue / g32_out (optional) from that value. */
+int b2_allreduce_bf16(const b2_xgpu_ctx* ctx, void* mc_base, long long wire_offset_bytes, long long n, int algo,
+                      float scale, const float* g32_in, float* g32_out, float* p32, float* mom, void* shadow_bf16,
+                      float lr, float momentum, float weight_decay, int first_step, int nblocks, void* stream);
 /* Broadcast through the NVSwitch multicast mapping: only the source rank stores, the switch replicates. */
 int b2_broadcast_mc(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long nbytes, int src,
                     int nblocks, void* stream);

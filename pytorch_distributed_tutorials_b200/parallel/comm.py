@@ -94,8 +94,11 @@ class P2PComm(_Base):
     PAD_COMM = 0      # signal pad used by kernels on the communication stream
     PAD_COMPUTE = 1   # signal pad used by kernels on the compute stream (SyncBN statistics, buffer broadcast)
 
-    def __init__(self, device, group=None, window_bytes=None, algo=None, nblocks=None):
+    def __init__(self, device, group=None, window_bytes=None, algo=None, nblocks=None, wire=None):
         super().__init__(group)
+        self.wire = (wire or os.environ.get("B200DDP_WIRE", "fp32")).lower()   # "fp32" | "bf16"
+        if self.wire not in ("fp32", "bf16"):
+            raise ValueError("gradient wire format must be fp32 or bf16")
         from .symm import SymmetricWindow
         self.device = torch.device(device)
         self.window_bytes = int(window_bytes)
@@ -145,19 +148,39 @@ class P2PComm(_Base):
             ev = torch.cuda.Event()
             ev.record(cur)
             st.wait_event(ev)
+        a = self.algo if algo is None else ALGOS[algo]
+        if a == ALGOS["multimem"] and not self.mc_base:
+            a = ALGOS["twoshot"]
+        if self.wire == "bf16":
+            return self._allreduce_bucket_bf16(bucket, sgd, a, st)
         off = self.window.offset_of(bucket.g32)
         if sgd is not None:
             lr, mu, wd, first = sgd
             args = (ptr(bucket.p32), ptr(bucket.mom), ptr(bucket.shadow), c_f(lr), c_f(mu), c_f(wd), int(first))
         else:
             args = (c_p(0), c_p(0), c_p(0), c_f(0.0), c_f(0.0), c_f(0.0), 0)
-        a = self.algo if algo is None else ALGOS[algo]
-        if a == ALGOS["multimem"] and not self.mc_base:
-            a = ALGOS["twoshot"]
         e = _lib.lib().b2_allreduce(ctypes.byref(self.window.ctx(self.PAD_COMM)), c_p(self.mc_base or 0), c_ll(off),
                                     c_ll(bucket.numel), a, c_f(1.0 / self.world), *args, int(self.write_grad),
                                     self.nblocks, c_p(st.cuda_stream))
         check(e, "b2_allreduce")
+        _lib.count_launch()
+
+    def _allreduce_bucket_bf16(self, bucket, sgd, a, st):
+        """bf16 wire: the kernel casts the fp32 bucket into a bf16 staging area of the window and reduces that."""
+        wire = getattr(bucket, "wire16", None)
+        if wire is None:
+            wire = bucket.wire16 = self.alloc_tensor(bucket.numel, torch.bfloat16)
+        if sgd is not None:
+            lr, mu, wd, first = sgd
+            args = (ptr(bucket.p32), ptr(bucket.mom), ptr(bucket.shadow), c_f(lr), c_f(mu), c_f(wd), int(first))
+        else:
+            args = (c_p(0), c_p(0), c_p(0), c_f(0.0), c_f(0.0), c_f(0.0), 0)
+        g_out = ptr(bucket.g32) if (self.write_grad or sgd is None) else c_p(0)
+        e = _lib.lib().b2_allreduce_bf16(ctypes.byref(self.window.ctx(self.PAD_COMM)), c_p(self.mc_base or 0),
+                                         c_ll(self.window.offset_of(wire)), c_ll(bucket.numel), a,
+                                         c_f(1.0 / self.world), ptr(bucket.g32), g_out, *args, self.nblocks,
+                                         c_p(st.cuda_stream))
+        check(e, "b2_allreduce_bf16")
         _lib.count_launch()
 
     def broadcast_window_(self, offset, nbytes, src=0, stream=None, pad=None):

@@ -45,7 +45,7 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
                  process_group=None, bucket_cap_mb=None, find_unused_parameters=False,
                  gradient_as_bucket_view=True, static_graph=False, backend=None, comm_algo=None,
-                 init_sync=True):
+                 init_sync=True, gradient_wire=None):
         super().__init__()
         if find_unused_parameters:
             raise NotImplementedError("find_unused_parameters is not supported (ResNets use every parameter)")
@@ -99,7 +99,10 @@ class DistributedDataParallel(nn.Module):
             total = sum((p.numel() + 63) // 64 * 64 for p in ordered) * 4
             buf_bytes = sum((b.numel() * b.element_size() + 255) // 256 * 256 for b in buffers)
             extra = 16 * MiB + 2 * buf_bytes + 2 * MiB  # staging, buffer region, SyncBN slots
-            self.comm = P2PComm(self.device, process_group, total + extra, algo=comm_algo)
+            wire = (gradient_wire or os.environ.get("B200DDP_WIRE", "fp32")).lower()
+            if wire == "bf16":
+                extra += total // 2 + MiB          # bf16 staging copy of every bucket
+            self.comm = P2PComm(self.device, process_group, total + extra, algo=comm_algo, wire=wire)
         elif backend == "local":
             self.comm = LocalComm(process_group)
         elif backend == "torch":

@@ -77,6 +77,33 @@ def _collectives(rank, world):
         res["sgd_%d" % n] = (b.p32 - pr).abs().max().item()
         res["sgd_%d_shadow" % n] = bool(torch.equal(b.shadow, b.p32.to(torch.bfloat16)))
         res["sgd_%d_grad" % n] = (b.g32 - avg).abs().max().item()
+    # bf16 wire format: fp32 accumulation of bf16-rounded inputs in rank order, rounded to bf16 once
+    comm16 = comm
+    comm16.wire = "bf16"
+    for n in [4096, 513024, 7213056]:
+        b = FakeBucket()
+        b.index, b.numel = 0, n
+        b.g32 = comm.grad_alloc(n)
+        for algo in algos:
+            if algo == "oneshot" and n > 524288:
+                continue
+            g = torch.Generator(device=dev).manual_seed(77 * rank + n % 13)
+            local = torch.randn(n, device=dev, generator=g)
+            b.g32.copy_(local)
+            parts = [torch.empty_like(local) for _ in range(world)]
+            dist.all_gather(parts, local)
+            acc = torch.zeros_like(local)
+            for q in parts:
+                acc += q.to(torch.bfloat16).float()
+            ref = (acc / world).to(torch.bfloat16).float()
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm16.allreduce_bucket(b, sgd=None, algo=algo)
+            comm16.finalize()
+            torch.cuda.synchronize()
+            res["bf16wire_%s_%d" % (algo, n)] = ((b.g32 - ref).abs().max() / ref.abs().max()).item()
+            dist.barrier()
+    comm.wire = "fp32"
     # broadcast of arbitrary tensors through the staging window
     t = [torch.full((1000, 3), float(rank + 1), device=dev), torch.arange(10, device=dev) + 100 * rank]
     comm.broadcast_(t, src=0)
@@ -97,6 +124,8 @@ def test_p2p_collectives_match_nccl(world):
                 assert v < 1e-5, (k, v)
             elif k.startswith("sgd_"):
                 assert v < 1e-5, (k, v)
+            elif k.startswith("bf16wire_"):
+                assert v < 1e-2, (k, v)      # at most one bf16 ulp (multimem's in-switch order may differ)
 
 
 def _ddp_train(rank, world, sync_bn):
