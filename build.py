@@ -23,7 +23,7 @@ NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nv
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--use_fast_math", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
          "-I" + os.path.join(ROOT, "include"), "-I" + CSRC, "--expt-relaxed-constexpr",
-         "-diag-suppress", "177"]
+         "-diag-suppress", "177"] + os.environ.get("B200DDP_NVCC_FLAGS", "").split()
 
 
 def _deps_hash(src):

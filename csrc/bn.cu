@@ -16,7 +16,10 @@
 namespace b2 {
 
 constexpr int kBnThreads = 256;
-constexpr int kMaxPartialBlocks = 592;  // 148 SMs x 4
+#ifndef B2_BN_BLOCKS_PER_SM
+#define B2_BN_BLOCKS_PER_SM 4
+#endif
+constexpr int kMaxPartialBlocks = 148 * B2_BN_BLOCKS_PER_SM;
 
 struct Vec8 {
   float v[8];
@@ -59,7 +62,7 @@ B2_DEVICE void block_reduce_store(float (&acc)[NACC][8], float* smem, float* par
 }
 
 // ------------------------------------------------------------------------------------------------ forward stats
-__global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* partial,
+__global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM) bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* partial,
                                                               long long M, int C, long long rows_per_blk) {
   extern __shared__ float smem[];
   const int C8 = C >> 3, RP = kBnThreads / C8;
@@ -216,7 +219,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 // ------------------------------------------------------------------------------------------------ backward
 // dz' = (dz_a [+ dz_b]) * (z > 0 if RELU).  Accumulates sum(dz') and sum(dz' * (y - mean)) per channel.
 template <bool RELU, bool TWO>
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
     bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
                          const __nv_bfloat16* __restrict__ z, const unsigned char* __restrict__ mask,
                          const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, float* partial,

@@ -43,6 +43,9 @@ struct ConvParams {
   // class (ph, pw): rows enumerate the class grid [N, rowH, rowW] and land on pixel (cls*i+ph, cls*j+pw) of dx.
   int kh0, kw0, kstep, nth, ntw;
   int cls, ph, pw, outH, outW;
+  // wgrad, k>1: the N axis is the flattened (tap, cin) axis of dW; every 64-column box of a tile belongs to one tap,
+  // so one dy tile is reused for up to four taps (flatN = 1).
+  int flatN;
 };
 
 constexpr int BM = 128;
@@ -532,6 +535,19 @@ __global__ void __launch_bounds__(kThreads2, 1)
           ih0 = h * p.stride - p.im2col_pad_h;
           iw0 = w * p.stride - p.im2col_pad_w;
         }
+        // wgrad over the flattened (tap, cin) axis: which tap / channel block each 64-column box of this tile is
+        int box_ci[BN / 64], box_kh[BN / 64], box_kw[BN / 64], box_valid = BN / 64;
+        if (KIND == WGRAD && IM2COL && p.flatN) {
+          box_valid = min(BN / 64, (p.Ncols - it.n0 + 63) / 64);  // boxes past the last tap are not loaded
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) {
+            const int col = it.n0 + 64 * j;
+            const int tp = col / p.tapC;
+            box_ci[j] = col - tp * p.tapC;
+            box_kh[j] = tp / p.KW;
+            box_kw[j] = tp - box_kh[j] * p.KW;
+          }
+        }
         for (int i = 0; i < it.nkb; ++i, ++g) {
           const int kb = it.kb_begin + i;
           const int s = g % C::kStages;
@@ -539,7 +555,9 @@ __global__ void __launch_bounds__(kThreads2, 1)
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sA = smem + s * C::kStageBytes;
           uint8_t* sB = sA + kABytes;
-          mbar_arrive_expect_tx(&full[s], kABytes + kBBytes);
+          uint32_t tx = kABytes + kBBytes;
+          if (KIND == WGRAD && IM2COL && p.flatN) tx = kABytes + box_valid * 8192;
+          mbar_arrive_expect_tx(&full[s], tx);
           if (KIND == FPROP) {
             if (IM2COL) {
               const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
@@ -569,11 +587,19 @@ __global__ void __launch_bounds__(kThreads2, 1)
             if (IM2COL) {
               int n, h, w;
               decode_pix(kb * BK, p.rowH, p.rowW, n, h, w);
-              const int kh = it.tap / p.KW, kw = it.tap - kh * p.KW;
+              const int bw = w * p.stride - p.im2col_pad_w, bh = h * p.stride - p.im2col_pad_h;
+              if (p.flatN) {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_im2col(sB + j * 8192, &tmB, &full[s], it.n0 + 64 * j, w * p.stride - p.im2col_pad_w,
-                                h * p.stride - p.im2col_pad_h, n, (uint16_t)kw, (uint16_t)kh);
+                for (int j = 0; j < BN / 64; ++j)
+                  if (j < box_valid)
+                    tma_load_im2col(sB + j * 8192, &tmB, &full[s], box_ci[j], bw, bh, n, (uint16_t)box_kw[j],
+                                    (uint16_t)box_kh[j]);
+              } else {
+                const int kh = it.tap / p.KW, kw = it.tap - kh * p.KW;
+#pragma unroll
+                for (int j = 0; j < BN / 64; ++j)
+                  tma_load_im2col(sB + j * 8192, &tmB, &full[s], it.n0 + 64 * j, bw, bh, n, (uint16_t)kw, (uint16_t)kh);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < BN / 64; ++j)
@@ -713,7 +739,8 @@ __global__ void __launch_bounds__(kThreads2, 1)
           if (ok) {
 #pragma unroll
             for (int q = 0; q < 8; ++q)
-              st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+              if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols)
+                st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
           }
         }
       }
@@ -914,8 +941,10 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
 extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes) {
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
-  const int bn = bn_for(Cin, WGRAD, Cout);
-  const long long tiles = (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
+  const bool flat = (g_impl == 2 && taps > 1 && g_act_mode != ACT_GATHER && !g_force_bn);
+  const int bn = flat ? 256 : bn_for(Cin, WGRAD, Cout);
+  const long long tiles = flat ? (long long)((Cout + BM - 1) / BM) * ((taps * Cin + 255) / 256)
+                               : (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
   long long want = ((g_impl == 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
   const long long wbytes = (long long)Cout * taps * Cin * 4;
   long long cap = ws_bytes / wbytes;
@@ -934,8 +963,9 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const int taps = KH * KW;
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
-  const int bn = bn_for(Cin, WGRAD, Cout);
   const int mode = pick_mode(WGRAD, KH, KW, stride, pad);
+  const bool flat = (g_impl == 2 && taps > 1 && mode == ACT_IM2COL && !g_force_bn);
+  const int bn = flat ? 256 : bn_for(Cin, WGRAD, Cout);
   const long long wcount = (long long)Cout * taps * Cin;
   if (ws_bytes < wcount * 4) return cudaErrorInvalidValue;
   const int splits = b2_conv_wgrad_splits(N, Ho, Wo, Cin, Cout, taps, ws_bytes);
@@ -959,7 +989,12 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   p.n_tiles = Cin / bn; p.m_tiles = (Cout + BM - 1) / BM;
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t ce;
-  if (g_impl == 2 && mode != ACT_GATHER) {
+  if (flat) {
+    p.flatN = 1;
+    p.Ncols = taps * Cin;
+    p.n_tiles = (p.Ncols + 255) / 256;
+    ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
+  } else if (g_impl == 2 && mode != ACT_GATHER) {
     ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * taps * splits, st);
   } else {
     dim3 grid(p.n_tiles, p.m_tiles, taps * splits);

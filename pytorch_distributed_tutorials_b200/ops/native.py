@@ -25,7 +25,7 @@ def scratch(device, key, numel, dtype=torch.float32):
 
 
 def bn_partial(device):
-    return scratch(device, "bn_partial", 592 * 2 * 2048)
+    return scratch(device, "bn_partial", 1184 * 2 * 2048)   # >= kMaxPartialBlocks * 2 * C_max
 
 
 class XgpuCtx(ctypes.Structure):

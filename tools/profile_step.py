@@ -21,7 +21,7 @@ def main():
     ap.add_argument("--rows", type=int, default=40)
     a = ap.parse_args()
     args = argparse.Namespace(model=a.model, batch=a.batch, image_size=a.image_size, sync_bn=False,
-                              bucket_cap_mb=None, no_fuse_optimizer=False, ref_variant="r1")
+                              bucket_cap_mb=None, no_fuse_optimizer=False, ref_variant="r1", no_graph=True)
     torch.cuda.set_device(0)
     step, ddp = (bench.build_ours if a.impl == "ours" else bench.build_reference)(args, 0, 1)
     dev = torch.device("cuda", 0)
