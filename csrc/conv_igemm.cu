@@ -449,7 +449,7 @@ static int pick_mode(int kind, int KH, int KW, int stride, int pad) {
 // pure GEMMs, im2col otherwise); strided dgrad is decomposed into output-pixel parity classes so that the im2col
 // walk never multiplies structural zeros.
 // =====================================================================================================
-constexpr int kThreads2 = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
+constexpr int kThreads2 = 224;  // warp 0 TMA (A), warp 1 MMA + TMEM alloc, warps 2-5 epilogue, warp 6 TMA (B)
 
 template <int BN>
 struct Cfg2 {
@@ -502,7 +502,7 @@ __global__ void __launch_bounds__(kThreads2, 1)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::kStages; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], 2);  // one arrive.expect_tx from each of the two TMA producer threads
       mbar_init(&empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -521,8 +521,10 @@ __global__ void __launch_bounds__(kThreads2, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
-    // ===================================================== TMA producer
+  if (warp == 0 || warp == 6) {
+    // ===================================================== TMA producers: warp 0 stages A, warp 6 stages B
+    // (two issuing threads: the MN-major operands of dgrad/wgrad need one TMA per 64-column box)
+    const bool doA = (warp == 0), doB = (warp == 6);
     if (lane == 0) {
       uint32_t g = 0;  // global k-block counter (smem ring position carries over from item to item)
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
@@ -555,35 +557,42 @@ __global__ void __launch_bounds__(kThreads2, 1)
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sA = smem + s * C::kStageBytes;
           uint8_t* sB = sA + kABytes;
-          uint32_t tx = kABytes + kBBytes;
-          if (KIND == WGRAD && IM2COL && p.flatN) tx = kABytes + box_valid * 8192;
-          mbar_arrive_expect_tx(&full[s], tx);
+          uint32_t txB = kBBytes;
+          if (KIND == WGRAD && IM2COL && p.flatN) txB = box_valid * 8192;
+          mbar_arrive_expect_tx(&full[s], doA ? kABytes : txB);
           if (KIND == FPROP) {
-            if (IM2COL) {
-              const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
-              const int kh = tp / p.KW, kw = tp - kh * p.KW;
-              tma_load_im2col(sA, &tmA, &full[s], cb * 64, iw0, ih0, in0, (uint16_t)kw, (uint16_t)kh);
+            if (doA) {
+              if (IM2COL) {
+                const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
+                const int kh = tp / p.KW, kw = tp - kh * p.KW;
+                tma_load_im2col(sA, &tmA, &full[s], cb * 64, iw0, ih0, in0, (uint16_t)kw, (uint16_t)kh);
+              } else {
+                tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
+              }
             } else {
-              tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
+              tma_load_2d(sB, &tmB, &full[s], kb * BK, it.n0);
             }
-            tma_load_2d(sB, &tmB, &full[s], kb * BK, it.n0);
           } else if (KIND == DGRAD) {
             const int tp = kb / p.cpb, cob = kb - tp * p.cpb;
             int tapidx = 0;
             if (IM2COL) {
               const int th = tp / p.ntw, tw = tp - th * p.ntw;
               tapidx = (p.kh0 + p.kstep * th) * p.KW + (p.kw0 + p.kstep * tw);
-              tma_load_im2col(sA, &tmA, &full[s], cob * 64, iw0, ih0, in0, (uint16_t)(p.ntw - 1 - tw),
-                              (uint16_t)(p.nth - 1 - th));
-            } else {
+              if (doA)
+                tma_load_im2col(sA, &tmA, &full[s], cob * 64, iw0, ih0, in0, (uint16_t)(p.ntw - 1 - tw),
+                                (uint16_t)(p.nth - 1 - th));
+            } else if (doA) {
               tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
             }
+            if (doB) {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sB + j * 8192, &tmB, &full[s], tapidx * p.tapC + it.n0 + 64 * j, cob * 64);
-          } else {
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(sB + j * 8192, &tmB, &full[s], tapidx * p.tapC + it.n0 + 64 * j, cob * 64);
+            }
+          } else if (doA) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
+          } else {
             if (IM2COL) {
               int n, h, w;
               decode_pix(kb * BK, p.rowH, p.rowW, n, h, w);
