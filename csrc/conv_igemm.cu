@@ -766,6 +766,285 @@ __global__ void __launch_bounds__(kThreads2, 1)
   if (warp == 1) tmem_free<2 * BN>(tmem_base);
 }
 
+// =====================================================================================================
+// v3: CTA pairs (cta_group::2).  Two CTAs of a 2-cluster (the two SMs of a TPC) compute one 256 x BN tile: each
+// stages its own 128 rows of A and BN/2 columns of B, the leader issues tcgen05.mma.cta_group::2 which reads
+// both CTAs' shared memory, and each CTA ends up with its 128 accumulator rows in its own TMEM.  Per SM the
+// tensor core does the same work as in v2 but reads one third less shared memory per MMA (4 KB + 4 KB instead of
+// 4 KB + 8 KB for BN = 256), which is what bounds v2 on the K-heavy layers.  Same persistent structure otherwise.
+// =====================================================================================================
+constexpr int kThreads3 = 192;  // warp 0 TMA, warp 1 MMA (leader CTA only) + TMEM alloc, warps 2-5 epilogue
+
+template <int BN>
+struct Cfg3 {
+  static constexpr int kABytes = BM * 128;
+  static constexpr int kBBytes = (BN / 2) * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 6 : 8;
+  static constexpr int kEpiBytes = 2 * BM * 128;
+  static constexpr int kSmem = kStages * kStageBytes + kEpiBytes + 1024 + 256;
+};
+
+template <int KIND, int AMODE, int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads3, 1)
+    igemm3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
+  using C = Cfg3<BN>;
+  constexpr bool IM2COL = (AMODE == ACT_IM2COL);
+  constexpr int BNH = BN / 2;  // B columns staged by each CTA
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + C::kStages * C::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + C::kEpiBytes);
+  uint64_t* full = bars;                          // used in the leader CTA (both CTAs' loads count there)
+  uint64_t* empty = bars + C::kStages;            // per CTA, signalled by the multicast commit
+  uint64_t* tfull = bars + 2 * C::kStages;        // [2] per CTA
+  uint64_t* tempty = bars + 2 * C::kStages + 2;   // [2] used in the leader CTA: 8 epilogue warps arrive
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();  // 0 = leader
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 2);   // one arrive.expect_tx per CTA of the pair
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 8);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  cluster_sync_all();
+  if (warp == 1) tmem_alloc_pair<2 * BN>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer (both CTAs)
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int item = pair; item < num_items; item += npairs) {
+        Item it = decode_item(p, item, KIND, BN);
+        // this CTA's share of the 256-row tile
+        const int m0 = (KIND == WGRAD ? it.m0 * 2 : it.m0 * 2) + 128 * (int)rank;  // items index 256-row tiles
+        const int nB = it.n0 + BNH * (int)rank;                                       // this CTA's B columns
+        int iw0 = 0, ih0 = 0, in0 = 0;
+        if (IM2COL && KIND != WGRAD) {
+          int n, h, w;
+          decode_pix(m0, p.rowH, p.rowW, n, h, w);
+          in0 = n;
+          ih0 = h * p.stride - p.im2col_pad_h;
+          iw0 = w * p.stride - p.im2col_pad_w;
+        }
+        for (int i = 0; i < it.nkb; ++i, ++g) {
+          const int kb = it.kb_begin + i;
+          const int s = g % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sA = smem + s * C::kStageBytes;
+          uint8_t* sB = sA + C::kABytes;
+          const uint32_t fb = mapa_cluster(smem_u32(&full[s]), 0);  // the leader's full barrier
+          mbar_arrive_expect_tx_cluster(fb, C::kABytes + C::kBBytes);
+          if (KIND == FPROP) {
+            if (IM2COL) {
+              const int tp = kb / p.cpb, cb = kb - tp * p.cpb;
+              const int kh = tp / p.KW, kw = tp - kh * p.KW;
+              tma_load_im2col_pair(sA, &tmA, fb, cb * 64, iw0, ih0, in0, (uint16_t)kw, (uint16_t)kh);
+            } else {
+              tma_load_2d_pair(sA, &tmA, fb, kb * BK, m0);
+            }
+            tma_load_2d_pair(sB, &tmB, fb, kb * BK, nB);   // W2d rows [nB, nB + BN/2): box {64, BN/2}
+          } else if (KIND == DGRAD) {
+            const int tp = kb / p.cpb, cob = kb - tp * p.cpb;
+            int tapidx = 0;
+            if (IM2COL) {
+              const int th = tp / p.ntw, tw = tp - th * p.ntw;
+              tapidx = (p.kh0 + p.kstep * th) * p.KW + (p.kw0 + p.kstep * tw);
+              tma_load_im2col_pair(sA, &tmA, fb, cob * 64, iw0, ih0, in0, (uint16_t)(p.ntw - 1 - tw),
+                                   (uint16_t)(p.nth - 1 - th));
+            } else {
+              tma_load_2d_pair(sA, &tmA, fb, kb * BK, m0);
+            }
+#pragma unroll
+            for (int j = 0; j < BNH / 64; ++j)
+              tma_load_2d_pair(sB + j * 8192, &tmB, fb, tapidx * p.tapC + nB + 64 * j, cob * 64);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) tma_load_2d_pair(sA + j * 8192, &tmA, fb, m0 + 64 * j, kb * BK);
+            if (IM2COL) {
+              int n, h, w;
+              decode_pix(kb * BK, p.rowH, p.rowW, n, h, w);
+              const int bw = w * p.stride - p.im2col_pad_w, bh = h * p.stride - p.im2col_pad_h;
+#pragma unroll
+              for (int j = 0; j < BNH / 64; ++j) {
+                // flattened (tap, cin) column of this box; columns past the last tap read tap 0 (never stored)
+                int col = nB + 64 * j;
+                if (col >= p.Ncols) col = 0;
+                const int tp = col / p.tapC, ci0 = col - tp * p.tapC;
+                const int kh = tp / p.KW, kw = tp - kh * p.KW;
+                tma_load_im2col_pair(sB + j * 8192, &tmB, fb, ci0, bw, bh, n, (uint16_t)kw, (uint16_t)kh);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < BNH / 64; ++j) tma_load_2d_pair(sB + j * 8192, &tmB, fb, nB + 64 * j, kb * BK);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer (leader CTA only)
+    if (lane == 0 && rank == 0) {
+      constexpr bool kAmn = (KIND == WGRAD);
+      constexpr bool kBmn = (KIND != FPROP);
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, kAmn, kBmn);
+      uint32_t g = 0, t = 0;
+      for (int item = pair; item < num_items; item += npairs, ++t) {
+        const Item it = decode_item(p, item, KIND, BN);
+        const uint32_t acc = t & 1;
+        mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int i = 0; i < it.nkb; ++i, ++g) {
+          const int s = g % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t aBase = smem_u32(smem + s * C::kStageBytes);
+          const uint32_t bBase = aBase + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = kAmn ? make_smem_desc_sw128(aBase + k * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(aBase + k * 32, 16, 1024);
+            const uint64_t db = kBmn ? make_smem_desc_sw128(bBase + k * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(bBase + k * 32, 16, 1024);
+            umma_bf16_pair(d_tmem, da, db, idesc, (i | k) != 0);
+          }
+          umma_commit_pair(&empty[s]);   // frees the stage in both CTAs
+        }
+        umma_commit_pair(&tfull[acc]);   // wakes the epilogue warps of both CTAs
+      }
+    }
+  } else {
+    // ===================================================== epilogue (both CTAs, own 128 rows)
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const bool store_thread = (threadIdx.x == 64);
+    const bool tma_epi = (KIND != WGRAD) && p.cls == 1;
+    uint32_t t = 0, panel_seq = 0;
+    for (int item = pair; item < num_items; item += npairs, ++t) {
+      const Item it = decode_item(p, item, KIND, BN);
+      const uint32_t acc = t & 1;
+      mbar_wait(&tfull[acc], (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
+      const int m0 = it.m0 * 2 + 128 * (int)rank;
+      const int m = m0 + row;
+      const bool ok = m < p.M;
+      if (KIND != WGRAD && tma_epi) {
+#pragma unroll 1
+        for (int pn = 0; pn < BN / 64; ++pn, ++panel_seq) {
+          if (it.n0 + pn * 64 >= p.Ncols) break;
+          uint8_t* buf = epi_smem + (panel_seq & 1) * (BM * 128);
+          if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld32(taddr + pn * 64 + h * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              if (p.bias) {
+                const int col = it.n0 + pn * 64 + h * 32 + q * 8;
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (col + e < p.Ncols)
+                    v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
+              }
+              uint4 o;
+              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              const int chunk = h * 4 + q;
+              *reinterpret_cast<uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+            }
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (store_thread) {
+            tma_store_2d(buf, &tmC, it.n0 + pn * 64, m0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+      } else if (KIND != WGRAD) {
+        long long orow_idx = m;
+        if (KIND == DGRAD && p.cls > 1 && ok) {
+          int n, i, j;
+          decode_pix(m, p.rowH, p.rowW, n, i, j);
+          orow_idx = ((long long)n * p.outH + (i * p.cls + p.ph)) * p.outW + (j * p.cls + p.pw);
+        }
+        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_ld + it.n0;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int col = it.n0 + c * 32 + q * 8;
+              if (col + 8 > p.Ncols) break;
+              uint4 o;
+              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              st_v4(orow + c * 32 + q * 8, o);
+            }
+          }
+        }
+      } else {
+        float* out = reinterpret_cast<float*>(p.out) + (size_t)it.split * p.split_stride;
+        float* orow = out + (size_t)m * p.out_ld + it.n0;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              if (it.n0 + c * 32 + q * 4 + 4 <= p.Ncols)
+                st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+          }
+        }
+      }
+      // release the accumulator stage: the leader's MMA warp counts the epilogue warps of both CTAs
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_cluster(smem_u32(&tempty[acc]), 0));
+    }
+  }
+
+  if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  tc_fence_before();
+  cluster_sync_all();   // neither CTA may free TMEM or exit while its partner still uses its memory / barriers
+  if (warp == 1) tmem_free_pair<2 * BN>(tmem_base);
+}
+
 static int g_num_sms = 0;
 static int num_sms() {
   if (!g_num_sms) {
@@ -814,7 +1093,42 @@ static cudaError_t launch2_mode(int mode, int bn, const CUtensorMap& tmA, const 
   return cudaErrorInvalidValue;
 }
 
-static int g_impl = 2;  // 1 = one tile per CTA (v1), 2 = persistent (v2)
+template <int KIND, int AMODE, int BN>
+static cudaError_t launch3(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int items,
+                           cudaStream_t st) {
+  auto kern = igemm3_kernel<KIND, AMODE, BN>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg3<BN>::kSmem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  CUtensorMap tmC = tmB;
+  if (KIND != WGRAD && p.cls == 1) {
+    int e = make_tmap_2d_bf16(&tmC, p.out, (uint64_t)p.Ncols, (uint64_t)p.M, 64, 128);
+    if (e) return (cudaError_t)e;
+  }
+  const int pairs = num_sms() / 2;
+  const int grid = 2 * (items < pairs ? items : pairs);
+  kern<<<grid, kThreads3, Cfg3<BN>::kSmem, st>>>(tmA, tmB, tmC, p, items);
+  return cudaGetLastError();
+}
+template <int KIND>
+static cudaError_t launch3_mode(int mode, int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
+                                int items, cudaStream_t st) {
+  if (mode == ACT_TILED) {
+    if (bn == 256) return launch3<KIND, ACT_TILED, 256>(tmA, tmB, p, items, st);
+    if (bn == 128) return launch3<KIND, ACT_TILED, 128>(tmA, tmB, p, items, st);
+  } else if (mode == ACT_IM2COL) {
+    if (bn == 256) return launch3<KIND, ACT_IM2COL, 256>(tmA, tmB, p, items, st);
+    if (bn == 128) return launch3<KIND, ACT_IM2COL, 128>(tmA, tmB, p, items, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+static int g_impl = 2;  // 1 = one tile per CTA (v1), 2 = persistent (v2), 3 = persistent CTA pairs where they fit
+// CTA pairs need a 256-row M tile and at least a 128-wide N tile.
+static bool use_pairs(int bn, long long m_extent) { return g_impl == 3 && (bn == 128 || bn == 256) && m_extent >= 256; }
 }  // namespace b2
 
 using namespace b2;
@@ -828,7 +1142,7 @@ extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
 // the channel count allows; wgrad only when Cout fills at least two M tiles.
 static int bn_for(int ncols, int kind = FPROP, int m_extent = 1 << 30) {
   if (g_force_bn) return pick_bn(ncols, g_force_bn);
-  if (g_impl == 2) {
+  if (g_impl >= 2) {
     const bool wide_ok = (kind != WGRAD) || m_extent >= 256;
     if (ncols % 256 == 0 && wide_ok) return 256;
   }
@@ -852,7 +1166,8 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, vo
   } else if ((e = make_tmap_2d_bf16(&tmA, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 128))) {
     return e;
   }
-  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)K, (uint64_t)Cout, 64, bn))) return e;
+  const bool pairs = use_pairs(bn, M) && mode != ACT_GATHER && Cout % bn == 0;
+  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)K, (uint64_t)Cout, 64, pairs ? bn / 2 : bn))) return e;
   ConvParams p{};
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
@@ -861,7 +1176,11 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, vo
   p.im2col_pad_h = pad; p.im2col_pad_w = pad; p.cls = 1; p.taps = KH * KW;
   p.n_tiles = (Cout + bn - 1) / bn; p.m_tiles = (M + BM - 1) / BM;
   cudaStream_t st = (cudaStream_t)stream;
-  if (g_impl == 2 && mode != ACT_GATHER) return launch2_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  if (pairs) {
+    p.m_tiles = (M + 2 * BM - 1) / (2 * BM);
+    return launch3_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  }
+  if (g_impl >= 2 && mode != ACT_GATHER) return launch2_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
   dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<FPROP>(mode, bn, tmA, tmB, p, grid, st);
 }
@@ -904,7 +1223,13 @@ static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int 
       p.kh0 = kh0; p.kw0 = kw0; p.kstep = stride; p.nth = nth; p.ntw = ntw;
       p.cls = stride; p.ph = ph; p.pw = pw; p.outH = H; p.outW = W; p.taps = KH * KW;
       p.n_tiles = Cin / bn; p.m_tiles = (p.M + BM - 1) / BM;
-      cudaError_t ce = launch2_mode<DGRAD>(ACT_IM2COL, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+      cudaError_t ce;
+      if (use_pairs(bn, p.M)) {
+        p.m_tiles = (p.M + 2 * BM - 1) / (2 * BM);
+        ce = launch3_mode<DGRAD>(ACT_IM2COL, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+      } else {
+        ce = launch2_mode<DGRAD>(ACT_IM2COL, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+      }
       if (ce != cudaSuccess) return ce;
     }
   }
@@ -919,7 +1244,7 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   const int cpb = (Cout + 63) / 64;
   const int bn = bn_for(Cin);
   cudaStream_t st = (cudaStream_t)stream;
-  if (stride > 1 && g_impl == 2 && g_act_mode != ACT_GATHER && Cout % 64 == 0)
+  if (stride > 1 && g_impl >= 2 && g_act_mode != ACT_GATHER && Cout % 64 == 0)
     return dgrad_strided_v2(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, Ho, Wo, bn, st);
   const int mode = pick_mode(DGRAD, KH, KW, stride, pad);
   CUtensorMap tmA, tmB;
@@ -941,7 +1266,11 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   p.kh0 = 0; p.kw0 = 0; p.kstep = 1; p.nth = KH; p.ntw = KW; p.cls = 1; p.outH = H; p.outW = W; p.taps = KH * KW;
   if (mode == ACT_IM2COL) p.stride = 1;
   p.n_tiles = Cin / bn; p.m_tiles = (M + BM - 1) / BM;
-  if (g_impl == 2 && mode != ACT_GATHER) return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  if (use_pairs(bn, M) && mode != ACT_GATHER) {
+    p.m_tiles = (M + 2 * BM - 1) / (2 * BM);
+    return launch3_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  }
+  if (g_impl >= 2 && mode != ACT_GATHER) return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
   dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<DGRAD>(mode, bn, tmA, tmB, p, grid, st);
 }
@@ -950,11 +1279,11 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
 extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes) {
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
-  const bool flat = (g_impl == 2 && taps > 1 && g_act_mode != ACT_GATHER && !g_force_bn);
+  const bool flat = (g_impl >= 2 && taps > 1 && g_act_mode != ACT_GATHER && !g_force_bn);
   const int bn = flat ? 256 : bn_for(Cin, WGRAD, Cout);
   const long long tiles = flat ? (long long)((Cout + BM - 1) / BM) * ((taps * Cin + 255) / 256)
                                : (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
-  long long want = ((g_impl == 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
+  long long want = ((g_impl >= 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
   const long long wbytes = (long long)Cout * taps * Cin * 4;
   long long cap = ws_bytes / wbytes;
   if (want > cap) want = cap;
@@ -973,7 +1302,7 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const long long kpix = (long long)N * Ho * Wo;
   const int kblocks = (int)((kpix + 63) / 64);
   const int mode = pick_mode(WGRAD, KH, KW, stride, pad);
-  const bool flat = (g_impl == 2 && taps > 1 && mode == ACT_IM2COL && !g_force_bn);
+  const bool flat = (g_impl >= 2 && taps > 1 && mode == ACT_IM2COL && !g_force_bn);
   const int bn = flat ? 256 : bn_for(Cin, WGRAD, Cout);
   const long long wcount = (long long)Cout * taps * Cin;
   if (ws_bytes < wcount * 4) return cudaErrorInvalidValue;
@@ -998,12 +1327,19 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   p.n_tiles = Cin / bn; p.m_tiles = (Cout + BM - 1) / BM;
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t ce;
-  if (flat) {
+  const bool pairs = use_pairs(bn, Cout) && Cout % 256 == 0 && mode != ACT_GATHER && (flat || taps == 1);
+  if (pairs) {   // 256 rows of Cout per CTA pair; N is the flattened (tap, cin) axis
+    p.flatN = 1;
+    p.Ncols = taps * Cin;
+    p.n_tiles = (p.Ncols + bn - 1) / bn;
+    p.m_tiles = Cout / 256;
+    ce = launch3_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
+  } else if (flat) {
     p.flatN = 1;
     p.Ncols = taps * Cin;
     p.n_tiles = (p.Ncols + 255) / 256;
     ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
-  } else if (g_impl == 2 && mode != ACT_GATHER) {
+  } else if (g_impl >= 2 && mode != ACT_GATHER) {
     ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * taps * splits, st);
   } else {
     dim3 grid(p.n_tiles, p.m_tiles, taps * splits);
