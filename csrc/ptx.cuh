@@ -159,10 +159,12 @@ B2_DEVICE uint32_t mapa_cluster(uint32_t smem_addr, uint32_t rank) {
   return r;
 }
 B2_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 B2_DEVICE void mbar_arrive_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr),
+  // (default .release.cta semantics: a cluster-scope release would cost a MEMBAR.GPU per k-block; the data itself is
+  // published by the TMA complete_tx on the same barrier)
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr),
                "r"(bytes)
                : "memory");
 }

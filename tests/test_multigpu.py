@@ -334,3 +334,43 @@ def test_peer_failure_is_detected_not_hung():
     assert msg is not None and ("CUDA" in msg or "launch failure" in msg or "trap" in msg.lower() or "error" in msg.lower()), out
     if status == "ok":
         assert out["seconds"] < 60
+
+
+def _generic_module(rank, world):
+    """An arbitrary nn.Module (no native engine): autograd hooks feed the same buckets / P2P kernels."""
+    import copy
+    import torch.distributed as dist
+    import torch.nn as nn
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Linear(64, 256), nn.ReLU(), nn.Linear(256, 256), nn.Tanh(), nn.Linear(256, 10)).to(dev)
+    ref = copy.deepcopy(net)
+    ours = DistributedDataParallel(net, device_ids=[rank], bucket_cap_mb=0.1)
+    theirs = TorchDDP(ref, device_ids=[rank])
+    o1 = optim.SGD(ours.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, fuse_with_backward=True)
+    o2 = torch.optim.SGD(theirs.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator(device=dev).manual_seed(3 + rank)
+    worst = 0.0
+    for _ in range(5):
+        x = torch.randn(32, 64, device=dev, generator=g)
+        y = torch.randint(0, 10, (32,), device=dev, generator=g)
+        for m, o in ((ours, o1), (theirs, o2)):
+            o.zero_grad()
+            nn.functional.cross_entropy(m(x), y).backward()
+            o.step()
+        torch.cuda.synchronize()
+        worst = max(worst, max((a - b).abs().max().item() for a, b in zip(ours.parameters(), theirs.parameters())))
+    flat = torch.cat([p.detach().reshape(-1) for p in ours.parameters()])
+    other = flat.clone()
+    dist.broadcast(other, 0)
+    return {"maxdiff": worst, "ident": bool(torch.equal(flat, other)), "buckets": len(ours.store.buckets)}
+
+
+def test_generic_module_through_p2p_backend_matches_torch_ddp():
+    _need(2)
+    for r in run_ranks(_generic_module, world=2, backend="b200", timeout=600):
+        assert r["ident"] and r["buckets"] > 1
+        assert r["maxdiff"] < 1e-4, r
