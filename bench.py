@@ -246,14 +246,22 @@ def main():
     def dev_step(i):
         return step(xs[i & 1], ys[i & 1])
 
-    for i in range(args.warmup):
-        dev_step(i)
-    barrier_sync(world)
-    _lib.reset_launches()
-    with ClockSampler(local_rank, 200) as clocks:
+    with ClockSampler(local_rank, 100) as clocks:   # started before warm-up: nvidia-smi needs a moment to come up
+        for i in range(args.warmup):
+            dev_step(i)
+        barrier_sync(world)
+        _lib.reset_launches()
+        t_begin = time.monotonic()
         ms_total = timed_region(dev_step, args.steps, world)
-    launches = _lib.launches()
-    clk = clocks.summary()
+        t_end = time.monotonic()
+        launches = _lib.launches()
+        if len(clocks.rows) < 2:                    # very short runs: keep the load on until two samples exist
+            t_wait = time.monotonic()
+            while len(clocks.rows) < 2 and time.monotonic() - t_wait < 3.0:
+                dev_step(0)
+            torch.cuda.synchronize()
+            t_end = time.monotonic()
+    clk = clocks.summary(t_begin, t_end)
     ms_step = ms_total / args.steps
     global_batch = args.batch * world
     value = global_batch / (ms_step / 1e3)

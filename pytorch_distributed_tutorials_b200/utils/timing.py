@@ -61,6 +61,7 @@ class ClockSampler:
     def __init__(self, gpu_index=0, period_ms=200):
         self.gpu, self.period_ms = gpu_index, period_ms
         self.rows = []
+        self.times = []
         self._proc = None
         self._thr = None
 
@@ -74,10 +75,12 @@ class ClockSampler:
             return self
 
         def pump():
+            import time
             for line in self._proc.stdout:
                 parts = [p.strip() for p in line.split(",")]
                 if len(parts) >= 9:
                     self.rows.append(parts)
+                    self.times.append(time.monotonic())
 
         self._thr = threading.Thread(target=pump, daemon=True)
         self._thr.start()
@@ -94,9 +97,17 @@ class ClockSampler:
             self._thr.join(timeout=2)
         return False
 
-    def summary(self):
+    def summary(self, t0=None, t1=None):
+        """Median SM clock / max clock / throttle reasons. With a (monotonic) window, samples inside it are used
+        when there are at least two; otherwise every sample taken since the sampler started (warm-up included:
+        the GPU is under the same load there)."""
+        rows = self.rows
+        if t0 is not None and t1 is not None:
+            inside = [r for r, t in zip(self.rows, self.times) if t0 <= t <= t1]
+            if len(inside) >= 2:
+                rows = inside
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for r in rows:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
