@@ -132,7 +132,8 @@ def main(argv=None):
         ddp_model.train()
         if args.reshuffle_each_epoch:
             train_sampler.set_epoch(epoch)
-        batches = DevicePrefetcher(train_loader, device) if use_cuda else train_loader
+        prefetch = use_cuda and os.environ.get("B200DDP_NO_PREFETCH", "0") != "1"
+        batches = DevicePrefetcher(train_loader, device) if prefetch else train_loader
         t0, seen = time.perf_counter(), 0
         for data in batches:
             inputs, labels = data[0].to(device), data[1].to(device)

@@ -36,7 +36,9 @@ class GraphedTrainStep:
         loss = self.criterion(self.model(x), y)
         loss.backward()
         self.optimizer.step()
-        return loss
+        # detached: a caller that keeps the loss around must not keep this step's autograd graph (and with it the
+        # per-parameter AccumulateGrad nodes, which remember the stream they were created on) alive into a capture
+        return loss.detach()
 
     def _hyper(self):
         g = self.optimizer.param_groups[0]
@@ -57,7 +59,8 @@ class GraphedTrainStep:
         n0 = _lib.launches()
         try:
             self.optimizer.zero_grad(set_to_none=True)
-            with torch.cuda.graph(g):
+            # thread_local: DataLoader pin-memory threads keep calling cudaHostAlloc while we capture
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 loss = self.criterion(self.model(sx), sy)
                 loss.backward()
                 self.optimizer.step()
@@ -85,7 +88,9 @@ class GraphedTrainStep:
             try:
                 entry = self._capture(x, y)
             except Exception as e:  # noqa: BLE001
-                warnings.warn("CUDA graph capture of the training step failed (%r); running eagerly" % (e,))
+                import traceback
+                warnings.warn("CUDA graph capture of the training step failed (%s: %s); running eagerly\n%s" %
+                              (type(e).__name__, str(e).splitlines()[0] if str(e) else "", traceback.format_exc()))
                 self.enabled = False
                 torch.cuda.synchronize()
                 return self._eager(x, y)
