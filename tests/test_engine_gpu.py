@@ -156,7 +156,10 @@ def test_graphed_train_step_matches_eager():
         ddp = DistributedDataParallel(net, device_ids=[0])
         opt = optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
         step = GraphedTrainStep(ddp, CrossEntropyLoss(), opt, warmup=2, enabled=graph)
-        losses = [float(step(xs[i % 3], ys[i % 3]).item()) for i in range(8)]
+        kept, losses = [], []
+        for i in range(8):
+            kept.append(step(xs[i % 3], ys[i % 3]))      # a caller holding on to the returned losses must not
+            losses.append(float(kept[-1].item()))        # keep autograd state alive into the capture
         runs.append((losses, [p.detach().clone() for p in ddp.parameters()], step.captures,
                      int(net.bn1.num_batches_tracked.item())))
     (l_g, p_g, caps, nbt_g), (l_e, p_e, _, nbt_e) = runs
