@@ -379,18 +379,23 @@ extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartial
 
 static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }
 
-extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
-                               const float* gamma,
-                               const float* beta, float* running_mean, float* running_var,
-                               long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
-                               float* invstd, float* scale_shift /*2C*/, float* partial, const b2_xgpu_ctx* xg,
-                               int xg_slot, void* stream) {
+// given_blocks > 0: `partial` already holds that many [2][C] rows of (sum, sum of squares) — produced by the
+// convolution's epilogue — and the statistics pass over y is skipped.
+static int bn_fwd_train_impl(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                             const float* gamma, const float* beta, float* running_mean, float* running_var,
+                             long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
+                             float* invstd, float* scale_shift /*2C*/, float* partial, int given_blocks,
+                             const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
   if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
   cudaStream_t st = (cudaStream_t)stream;
-  long long rpb;
-  const int nblk = plan_blocks(M, C, &rpb);
-  const int RP = kBnThreads / (C / 8);
-  bn_stats_kernel<<<nblk, kBnThreads, 2 * RP * C * sizeof(float), st>>>((const __nv_bfloat16*)y, partial, M, C, rpb);
+  int nblk = given_blocks;
+  if (given_blocks <= 0) {
+    long long rpb;
+    nblk = plan_blocks(M, C, &rpb);
+    const int RP = kBnThreads / (C / 8);
+    bn_stats_kernel<<<nblk, kBnThreads, 2 * RP * C * sizeof(float), st>>>((const __nv_bfloat16*)y, partial, M, C,
+                                                                         rpb);
+  }
   XgpuCtx ctx = xgpu_from_c(xg);
   bn_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(
       partial, nblk, C, (float)M, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, mean,
@@ -406,6 +411,25 @@ extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, void* re
   else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   return cudaGetLastError();
+}
+
+extern "C" int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                               const float* gamma, const float* beta, float* running_mean, float* running_var,
+                               long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
+                               float* invstd, float* scale_shift, float* partial, const b2_xgpu_ctx* xg, int xg_slot,
+                               void* stream) {
+  return bn_fwd_train_impl(y, res, z, relu_mask, M, C, gamma, beta, running_mean, running_var, num_batches_tracked,
+                           momentum, eps, relu, mean, invstd, scale_shift, partial, 0, xg, xg_slot, stream);
+}
+extern "C" int b2_bn_fwd_train_partial(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                                       const float* gamma, const float* beta, float* running_mean,
+                                       float* running_var, long long* num_batches_tracked, float momentum, float eps,
+                                       int relu, float* mean, float* invstd, float* scale_shift, float* partial,
+                                       int partial_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  if (partial_blocks <= 0) return cudaErrorInvalidValue;
+  return bn_fwd_train_impl(y, res, z, relu_mask, M, C, gamma, beta, running_mean, running_var, num_batches_tracked,
+                           momentum, eps, relu, mean, invstd, scale_shift, partial, partial_blocks, xg, xg_slot,
+                           stream);
 }
 
 extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma,

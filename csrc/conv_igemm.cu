@@ -46,6 +46,9 @@ struct ConvParams {
   // wgrad, k>1: the N axis is the flattened (tap, cin) axis of dW; every 64-column box of a tile belongs to one tap,
   // so one dy tile is reused for up to four taps (flatN = 1).
   int flatN;
+  // fprop (v2): per-CTA partial BatchNorm statistics of the bf16 output, [gridDim][2][Ncols] fp32 (sum, sum of
+  // squares), accumulated tile by tile in a fixed order -> deterministic. nullptr = not requested.
+  float* stats;
 };
 
 constexpr int BM = 128;
@@ -449,7 +452,13 @@ static int pick_mode(int kind, int KH, int KW, int stride, int pad) {
 // pure GEMMs, im2col otherwise); strided dgrad is decomposed into output-pixel parity classes so that the im2col
 // walk never multiplies structural zeros.
 // =====================================================================================================
-constexpr int kThreads2 = 224;  // warp 0 TMA (A), warp 1 MMA + TMEM alloc, warps 2-5 epilogue, warp 6 TMA (B)
+// warp 0 TMA (A), warp 1 MMA + TMEM alloc, warps 2-5 and 7-10 epilogue, warp 6 TMA (B)
+constexpr int kThreads2 = 352;
+constexpr int kEpiThreads2 = 256;
+constexpr int kThreads2W = 224;  // wgrad (fp32 stores straight from registers) runs with the first epilogue group only
+// fprop with fused BatchNorm statistics: 4 or 8 more warps (11..) read the bf16 output panels back from shared memory
+template <int BN>
+constexpr int kStatWarps2 = (BN == 64) ? 4 : 8;
 
 template <int BN>
 struct Cfg2 {
@@ -481,7 +490,7 @@ B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn) {
 }
 
 template <int KIND, int AMODE, int BN>
-__global__ void __launch_bounds__(kThreads2, 1)
+__global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2), 1)
     igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
   using C = Cfg2<BN>;
@@ -507,7 +516,7 @@ __global__ void __launch_bounds__(kThreads2, 1)
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 4);  // one arrival per epilogue warp
+      mbar_init(&tempty[a], KIND == WGRAD ? 4 : kEpiThreads2 / 32);  // one arrival per epilogue warp
     }
     fence_mbar_init();
   }
@@ -651,12 +660,110 @@ __global__ void __launch_bounds__(kThreads2, 1)
         umma_commit(&tfull[acc]);
       }
     }
+  } else if (warp >= 11) {
+    // ===================================================== statistics warps 11.. (fprop with p.stats only)
+    // BatchNorm statistics of exactly the bf16 values being stored, read back from the epilogue's shared-memory
+    // panels while the epilogue warps convert the next panel. A warp pair owns one 64-column panel index (and one
+    // of R row groups of it): each thread sums one 16-byte chunk (8 channels) over every 8th row; lanes g = 0..7
+    // read rows = g (mod 8), eight different swizzle phases, so the 128-bit loads are conflict free (rows past M
+    // are zero: their A rows were zero-filled). The sums stay in registers until the CTA moves to another n-tile;
+    // a transposing butterfly over the 8 lanes then leaves lane g with channel chunk*8+g, which goes to
+    // stats[R*cta + row group][2][Ncols].
+    if (KIND == FPROP && p.stats) {
+      constexpr int P = BN / 64, NSW = kStatWarps2<BN>, R = NSW / (2 * P), NLD = (BM / R) / 8;
+      constexpr int CNT = kEpiThreads2 + 64 * R;
+      const int sw = warp - 11, g = lane & 7;
+      const int pair = sw >> 1, pn = pair % P, rg = pair / P;
+      const int chunk = (sw & 1) * 4 + (lane >> 3);
+      {
+        float4* z = reinterpret_cast<float4*>(p.stats + (size_t)blockIdx.x * R * 2 * p.Ncols);
+        for (int i = threadIdx.x - kThreads2; i < R * 2 * p.Ncols / 4; i += NSW * 32)
+          z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      asm volatile("bar.sync 10, %0;" ::"n"(NSW * 32) : "memory");
+      // the panel buffers start out free: one arrival on each "free" barrier the epilogue waits on first
+      if (P == 1) {
+        asm volatile("bar.arrive 6, %0;" ::"n"(CNT) : "memory");
+        asm volatile("bar.arrive 7, %0;" ::"n"(CNT) : "memory");
+      } else if (pn >= P - 2) {
+        asm volatile("bar.arrive %0, %1;" ::"r"(6 + pn), "n"(CNT) : "memory");
+      }
+      const bool rmw = (gridDim.x % p.n_tiles) != 0;   // this CTA comes back to an n-tile it has already flushed
+      float a[8], b[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) a[e] = b[e] = 0.f;
+      int st_n0 = -1;
+      auto flush = [&]() {
+        if (st_n0 < 0) return;
+#pragma unroll
+        for (int w = 4; w >= 1; w >>= 1) {
+          const bool up = (g & w) != 0;
+#pragma unroll
+          for (int j = 0; j < w; ++j) {
+            const float sa = up ? a[j] : a[j + w], ka = up ? a[j + w] : a[j];
+            const float sb = up ? b[j] : b[j + w], kb = up ? b[j + w] : b[j];
+            a[j] = ka + __shfl_xor_sync(0xffffffffu, sa, w);
+            b[j] = kb + __shfl_xor_sync(0xffffffffu, sb, w);
+          }
+        }
+        const int gc = st_n0 + pn * 64 + chunk * 8 + g;
+        if (gc < p.Ncols) {
+          float* dst = p.stats + (size_t)(blockIdx.x * R + rg) * 2 * p.Ncols + gc;
+          if (rmw) {
+            dst[0] += a[0];
+            dst[p.Ncols] += b[0];
+          } else {
+            dst[0] = a[0];
+            dst[p.Ncols] = b[0];
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) a[e] = b[e] = 0.f;
+      };
+      uint32_t t = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
+        const Item it = decode_item(p, item, KIND, BN);
+        if (it.n0 != st_n0) {
+          flush();
+          st_n0 = it.n0;
+        }
+        const uint32_t bsel = (P == 1) ? (t & 1) : (pn & 1);
+        const uint32_t slot = (P == 1) ? bsel : pn;
+        asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(CNT) : "memory");   // panel written
+        const uint32_t src =
+            smem_u32(epi_smem) + bsel * (BM * 128) + (rg * (BM / R) + g) * 128 + ((chunk ^ g) << 4);
+        uint4 w[NLD];
+#pragma unroll
+        for (int i = 0; i < NLD; ++i) w[i] = ld_shared_v4(src + i * 1024);
+        __threadfence_block();                                                    // reads done before the hand-back
+        asm volatile("bar.arrive %0, %1;" ::"r"(6 + slot), "n"(CNT) : "memory");   // panel buffer free again
+#pragma unroll
+        for (int i = 0; i < NLD; ++i) {
+          const uint32_t ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float lo = __uint_as_float(ww[e] << 16), hi = __uint_as_float(ww[e] & 0xffff0000u);
+            a[2 * e] += lo;
+            b[2 * e] = fmaf(lo, lo, b[2 * e]);
+            a[2 * e + 1] += hi;
+            b[2 * e + 1] = fmaf(hi, hi, b[2 * e + 1]);
+          }
+        }
+      }
+      flush();
+    }
   } else {
-    // ===================================================== epilogue warps 2..5 (TMEM lane quadrant = warp % 4)
+    // ===================================================== epilogue warps 2..5 and 7..10 (TMEM lane quadrant =
+    // warp % 4). The second group doubles the drain rate: for bf16 outputs group eg converts columns
+    // [32*eg, 32*eg+32) of every 64-column panel (wgrad is launched with the first group only).
+    const int eg = warp >= 7 ? 1 : 0;
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const bool store_thread = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
     const bool tma_epi = (KIND != WGRAD) && p.cls == 1;
+    const bool with_stats = (KIND == FPROP) && p.stats != nullptr;
+    constexpr int P = BN / 64;
+    constexpr int CNT = kEpiThreads2 + 64 * (kStatWarps2<BN> / (2 * P));
     uint32_t t = 0, panel_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
       const Item it = decode_item(p, item, KIND, BN);
@@ -669,37 +776,44 @@ __global__ void __launch_bounds__(kThreads2, 1)
       if (KIND != WGRAD && tma_epi) {
         // TMEM -> registers -> bf16 -> 128B-swizzled shared panel -> TMA store (full-line writes; the store clips
         // rows >= M and columns >= Ncols). Panels are double buffered.
+        const uint32_t swz = (row & 7) << 4;
 #pragma unroll 1
-        for (int pn = 0; pn < BN / 64; ++pn, ++panel_seq) {
+        for (int pn = 0; pn < P; ++pn, ++panel_seq) {
           if (it.n0 + pn * 64 >= p.Ncols) break;
-          uint8_t* buf = epi_smem + (panel_seq & 1) * (BM * 128);
-          if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          asm volatile("bar.sync 1, 128;" ::: "memory");  // the buffer's previous store has finished reading it
+          const uint32_t bsel = panel_seq & 1;
+          uint8_t* buf = epi_smem + bsel * (BM * 128);
+          uint32_t v[32];
+          tmem_ld32(taddr + pn * 64 + eg * 32, v);
+          tmem_ld_wait();
+          if (p.bias) {
+            const int col = it.n0 + pn * 64 + eg * 32;
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            uint32_t v[32];
-            tmem_ld32(taddr + pn * 64 + h * 32, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              if (p.bias) {
-                const int col = it.n0 + pn * 64 + h * 32 + q * 8;
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                  if (col + e < p.Ncols)
-                    v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
-              }
-              uint4 o;
-              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
-              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
-              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
-              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
-              const int chunk = h * 4 + q;  // 16-byte chunk index inside the 128-byte panel row
-              *reinterpret_cast<uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
-            }
+            for (int e = 0; e < 32; ++e)
+              if (col + e < p.Ncols) v[e] = __float_as_uint(__uint_as_float(v[e]) + __ldg(p.bias + col + e));
           }
+          uint4 o[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            o[q].x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+            o[q].y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+            o[q].z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+            o[q].w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+          }
+          // the panel buffer is needed only now: its previous TMA store has finished reading it ...
+          if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
+          if (with_stats)   // ... and so have the statistics warps
+            asm volatile("bar.sync %0, %1;" ::"r"(6 + (P == 1 ? bsel : (pn + P - 2) % P)), "n"(CNT) : "memory");
+          uint8_t* prow = buf + row * 128;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)  // 16-byte chunk eg*4+q of the 128-byte panel row, XOR-swizzled by the row phase
+            *reinterpret_cast<uint4*>(prow + ((uint32_t((eg * 4 + q) << 4)) ^ swz)) = o[q];
           fence_proxy_async_smem();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (with_stats) {                                  // panel complete: hand it to the statistics warps
+            __threadfence_block();
+            asm volatile("bar.arrive %0, %1;" ::"r"(2 + (P == 1 ? bsel : pn)), "n"(CNT) : "memory");
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
           if (store_thread) {
             tma_store_2d(buf, &tmC, it.n0 + pn * 64, it.m0);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -714,7 +828,7 @@ __global__ void __launch_bounds__(kThreads2, 1)
         }
         __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_ld + it.n0;
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = eg; c < BN / 32; c += 2) {
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
@@ -1072,7 +1186,8 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     configured = true;
   }
   const int grid = items < num_sms() ? items : num_sms();
-  kern<<<grid, kThreads2, Cfg2<BN>::kSmem, st>>>(tmA, tmB, tmC, p, items);
+  const int threads = (KIND == FPROP && p.stats) ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2);
+  kern<<<grid, threads, Cfg2<BN>::kSmem, st>>>(tmA, tmB, tmC, p, items);
   return cudaGetLastError();
 }
 template <int KIND, int AMODE>
@@ -1126,6 +1241,7 @@ static cudaError_t launch3_mode(int mode, int bn, const CUtensorMap& tmA, const 
   return cudaErrorInvalidValue;
 }
 
+static int g_fuse_stats = 1;  // fprop epilogue also produces the BatchNorm statistics partials
 static int g_impl = 2;  // 1 = one tile per CTA (v1), 2 = persistent (v2), 3 = persistent CTA pairs where they fit
 // CTA pairs need a 256-row M tile and at least a 128-wide N tile.
 static bool use_pairs(int bn, long long m_extent) { return g_impl == 3 && (bn == 128 || bn == 256) && m_extent >= 256; }
@@ -1149,8 +1265,12 @@ static int bn_for(int ncols, int kind = FPROP, int m_extent = 1 << 30) {
   return pick_bn(ncols, 0);
 }
 
-extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
-                             int Cout, int KH, int KW, int stride, int pad, void* stream) {
+// stats / stats_blocks: optional. When the persistent kernel runs, it also leaves per-CTA partial BatchNorm
+// statistics of y in stats ([*stats_blocks][2][Cout] fp32); *stats_blocks == 0 means "not produced, run bn_stats".
+static int conv_fprop_impl(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
+                           int Cout, int KH, int KW, int stride, int pad, float* stats, int* stats_blocks,
+                           void* stream) {
+  if (stats_blocks) *stats_blocks = 0;
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * Ho * Wo, K = KH * KW * Cin;
@@ -1180,10 +1300,30 @@ extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, vo
     p.m_tiles = (M + 2 * BM - 1) / (2 * BM);
     return launch3_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
   }
-  if (g_impl >= 2 && mode != ACT_GATHER) return launch2_mode<FPROP>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  if (g_impl >= 2 && mode != ACT_GATHER) {
+    const int items = p.n_tiles * p.m_tiles;
+    if (stats && stats_blocks && g_fuse_stats && Cout % bn == 0) {   // every 64-column panel of every tile exists
+      const int grid = items < num_sms() ? items : num_sms();   // must match launch2()
+      // one (256-wide tile) or two partial rows per CTA, zeroed by the kernel itself
+      p.stats = stats;
+      *stats_blocks = (bn == 256 ? 1 : 2) * grid;
+    }
+    return launch2_mode<FPROP>(mode, bn, tmA, tmB, p, items, st);
+  }
   dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<FPROP>(mode, bn, tmA, tmB, p, grid, st);
 }
+
+extern "C" int b2_conv_fprop(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin,
+                             int Cout, int KH, int KW, int stride, int pad, void* stream) {
+  return conv_fprop_impl(x, w, bias, y, N, H, W, Cin, Cout, KH, KW, stride, pad, nullptr, nullptr, stream);
+}
+extern "C" int b2_conv_fprop_stats(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
+                                   int KH, int KW, int stride, int pad, float* stats, int* stats_blocks,
+                                   void* stream) {
+  return conv_fprop_impl(x, w, nullptr, y, N, H, W, Cin, Cout, KH, KW, stride, pad, stats, stats_blocks, stream);
+}
+extern "C" void b2_conv_set_fuse_stats(int on) { g_fuse_stats = on; }
 
 // Strided dgrad, one output-pixel parity class at a time (persistent kernel + TMA im2col over dy).
 static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,

@@ -308,6 +308,11 @@ B2_DEVICE uint32_t ld_relaxed_sys(const uint32_t* p) {
 B2_DEVICE void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 
 // 16-byte streaming loads/stores used on peer pointers (no L1 allocation: peer data is read once).
+B2_DEVICE uint4 ld_shared_v4(uint32_t saddr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+  return v;
+}
 B2_DEVICE uint4 ld_nc_v4(const void* p) {
   uint4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"

@@ -38,6 +38,14 @@ typedef struct b2_xgpu_ctx {
  * ---------------------------------------------------------------------------------------------- */
 int b2_conv_fprop(const void* x, const void* w, const float* bias /*nullable, fp32[Cout]*/, void* y, int N, int H,
                   int W, int Cin, int Cout, int KH, int KW, int stride, int pad, void* stream);
+/* fprop that also leaves the BatchNorm statistics of y behind (fused into the persistent kernel:
+ * eight extra warps read the bf16 output panels back from shared memory while the epilogue warps convert the next one).
+ * stats receives [*stats_blocks][2][Cout] fp32 partial (sum, sum of squares) rows, to be handed to
+ * b2_bn_fwd_train_partial; *stats_blocks == 0 means the active kernel variant did not produce them. stats must hold
+ * 4 * (number of SMs) * 2 * Cout floats. */
+int b2_conv_fprop_stats(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                        int stride, int pad, float* stats, int* stats_blocks, void* stream);
+void b2_conv_set_fuse_stats(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.
@@ -66,6 +74,12 @@ int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, lo
                     const float* gamma, const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
                     float momentum, float eps, int relu, float* mean, float* invstd, float* scale_shift,
                     float* partial, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
+/* Same, but the statistics partials come from b2_conv_fprop_stats (partial_blocks rows of [2][C]). */
+int b2_bn_fwd_train_partial(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,
+                            const float* gamma, const float* beta, float* running_mean, float* running_var,
+                            long long* num_batches_tracked, float momentum, float eps, int relu, float* mean,
+                            float* invstd, float* scale_shift, float* partial, int partial_blocks,
+                            const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long M, int C, const float* gamma, const float* beta,
                    const float* running_mean, const float* running_var, float eps, int relu, float* scale_shift,
                    void* stream);

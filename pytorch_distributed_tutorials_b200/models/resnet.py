@@ -249,9 +249,15 @@ class ResNetEngine:
         return convops.conv_fprop(x, self._w16(conv.weight), conv.stride[0], conv.padding[0])
 
     def _unit(self, x, conv, bn, relu, res, training, tape):
-        y = self._conv(x, conv)
+        blocks = 0
+        if training or bn.running_mean is None:
+            # training-mode BN: the conv epilogue accumulates the statistics, no separate pass over y
+            y, blocks = convops.conv_fprop_stats(x, self._w16(conv.weight), conv.stride[0], conv.padding[0],
+                                                 native.bn_partial(self.device))
+        else:
+            y = self._conv(x, conv)
         mask = self._new_mask(y) if (tape is not None and relu) else None
-        z = self._bn_apply(y, bn, relu, res, training, mask)
+        z = self._bn_apply(y, bn, relu, res, training, mask, blocks)
         if tape is not None:
             tape.append(_Rec(x, y, mask, conv, bn, relu))
         return z
@@ -261,7 +267,7 @@ class ResNetEngine:
         """ReLU bit mask (1 bit / element): what backward needs instead of re-reading the bf16 output."""
         return torch.empty(y.numel() // 8, dtype=torch.uint8, device=y.device)
 
-    def _bn_apply(self, y, bn, relu, res, training, mask=None):
+    def _bn_apply(self, y, bn, relu, res, training, mask=None, partial_blocks=0):
         st = self._bn(bn)
         use_batch_stats = training or bn.running_mean is None
         if use_batch_stats:
@@ -270,7 +276,8 @@ class ResNetEngine:
             return native.bn_fwd_train(y, res, bn.weight, bn.bias, bn.running_mean if track else None,
                                        bn.running_var if track else None,
                                        bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
-                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot, mask)
+                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot, mask,
+                                       partial_blocks)
         return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
                                   st.scale_shift)
 
@@ -282,11 +289,15 @@ class ResNetEngine:
         if not w_ohwi.is_contiguous():
             w_ohwi = w_ohwi.contiguous()
         native.stem_pack_w(w_ohwi, self.stem_wp)                # fp32 OHWI [64,147] -> bf16 [64,192]
-        y2d = convops.gemm_nt(a, self.stem_wp)
+        blocks = 0
+        if training or m.bn1.running_mean is None:
+            y2d, blocks = convops.gemm_nt_stats(a, self.stem_wp, native.bn_partial(self.device))
+        else:
+            y2d = convops.gemm_nt(a, self.stem_wp)
         n = x.shape[0]
         y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
         mask = self._new_mask(y) if tape is not None else None
-        z = self._bn_apply(y, m.bn1, True, None, training, mask)
+        z = self._bn_apply(y, m.bn1, True, None, training, mask, blocks)
         if tape is not None:
             tape.append(_Rec(None, y, mask, m.conv1, m.bn1, True, stem_a=a))
         return z

@@ -4,6 +4,8 @@ Stands in for ``aten::convolution`` / ``convolution_backward`` that the referenc
 torchvision's ResNet (reference resnet/main.py:76,121,123).  Activations are bf16 NHWC (torch
 ``channels_last``), weights bf16 OHWI (``channels_last`` of the OIHW parameter), weight gradients fp32 OHWI.
 """
+import ctypes
+
 import torch
 import torch.nn.functional as F
 
@@ -84,6 +86,34 @@ def conv_fprop(x, w, stride, pad, bias=None):
     _lib.check(e, "b2_conv_fprop")
     _lib.count_launch()
     return y
+
+
+def conv_fprop_stats(x, w, stride, pad, partial):
+    """conv_fprop whose epilogue also accumulates the BatchNorm statistics of y into ``partial``.
+    Returns (y, blocks): ``blocks`` rows of [2][Cout] partial sums were written (0: not produced by this variant)."""
+    N, H, W, Cin, Cout, KH, KW, s, p = _geom(x, w, stride, pad)
+    Ho, Wo = (H + 2 * p - KH) // s + 1, (W + 2 * p - KW) // s + 1
+    assert _is_cl(x) and _is_cl(w), "conv_fprop expects channels_last operands"
+    y = torch.empty((N, Cout, Ho, Wo), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    blocks = ctypes.c_int(0)
+    e = _lib.lib().b2_conv_fprop_stats(_lib.ptr(x), _lib.ptr(w), _lib.ptr(y), N, H, W, Cin, Cout, KH, KW, s, p,
+                                       _lib.ptr(partial), ctypes.byref(blocks), _lib.stream_ptr())
+    _lib.check(e, "b2_conv_fprop_stats")
+    _lib.count_launch()
+    return y, blocks.value
+
+
+def gemm_nt_stats(a, w, partial):
+    """gemm_nt (no bias) + per-column statistics partials of the bf16 result (stem convolution)."""
+    M, K = a.shape
+    N = w.shape[0]
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    blocks = ctypes.c_int(0)
+    e = _lib.lib().b2_conv_fprop_stats(_lib.ptr(a), _lib.ptr(w), _lib.ptr(y), M, 1, 1, K, N, 1, 1, 1, 0,
+                                       _lib.ptr(partial), ctypes.byref(blocks), _lib.stream_ptr())
+    _lib.check(e, "b2_conv_fprop_stats(gemm_nt)")
+    _lib.count_launch()
+    return y, blocks.value
 
 
 def conv_dgrad(dy, w, x_shape, stride, pad):

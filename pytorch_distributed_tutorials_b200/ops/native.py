@@ -46,11 +46,20 @@ def _mc(t):
 
 # ------------------------------------------------------------------------------------------------ batch norm
 def bn_fwd_train(y, res, gamma, beta, running_mean, running_var, nbt, momentum, eps, relu, mean, invstd,
-                 scale_shift, xg=None, xg_slot=0, mask=None):
+                 scale_shift, xg=None, xg_slot=0, mask=None, partial_blocks=0):
     """aten::native_batch_norm (training) + relu_ + add_ fused. Returns z. ``mask`` (uint8 [M*C/8], optional)
     receives one bit per element where the ReLU passed."""
     M, C = _mc(y)
     z = torch.empty_like(y)
+    if partial_blocks > 0:   # statistics partials already produced by the convolution's epilogue
+        e = _lib.lib().b2_bn_fwd_train_partial(ptr(y), ptr(res), ptr(z), ptr(mask), c_ll(M), C, ptr(gamma), ptr(beta),
+                                               ptr(running_mean), ptr(running_var), ptr(nbt), c_f(momentum),
+                                               c_f(eps), int(relu), ptr(mean), ptr(invstd), ptr(scale_shift),
+                                               ptr(bn_partial(y.device)), int(partial_blocks), _xg(xg), xg_slot,
+                                               stream_ptr())
+        check(e, "b2_bn_fwd_train_partial")
+        count_launch(2)
+        return z
     e = _lib.lib().b2_bn_fwd_train(ptr(y), ptr(res), ptr(z), ptr(mask), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
                                    ptr(running_var), ptr(nbt), c_f(momentum), c_f(eps), int(relu), ptr(mean),
                                    ptr(invstd), ptr(scale_shift), ptr(bn_partial(y.device)), _xg(xg), xg_slot,

@@ -203,3 +203,26 @@ def test_stem_conv_via_im2col():
     ref_dw = conv.ref_wgrad(x.to(torch.bfloat16).float(), dy.float().view(3, ho, wo, 64).permute(0, 3, 1, 2),
                             w.shape, 2, 3)
     assert _rel(dw.permute(0, 3, 1, 2), ref_dw) < 5e-3
+
+
+@pytest.mark.parametrize("ci,co,k,s,p,H,N", [(64, 256, 1, 1, 0, 56, 4), (256, 256, 3, 1, 1, 14, 8),
+                                               (512, 2048, 1, 1, 0, 7, 5), (128, 128, 3, 2, 1, 28, 3),
+                                               (256, 64, 1, 1, 0, 56, 2), (64, 64, 3, 1, 1, 56, 16),
+                                               (512, 2048, 1, 1, 0, 7, 64), (256, 512, 1, 2, 0, 56, 16)])
+def test_conv_epilogue_bn_statistics(ci, co, k, s, p, H, N):
+    """The persistent fprop kernel also accumulates per-channel sum / sum of squares of the bf16 output."""
+    from pytorch_distributed_tutorials_b200.ops import conv, native
+    torch.manual_seed(7)
+    x = _bf(torch.randn(N, ci, H, H, device=DEV))
+    w = _bf(torch.randn(co, ci, k, k, device=DEV) / (ci * k * k) ** 0.5)
+    partial = native.bn_partial(torch.device(DEV))
+    partial.fill_(float("nan"))                       # the kernel must zero what it uses
+    y, blocks = conv.conv_fprop_stats(x, w, s, p, partial)
+    assert blocks > 0
+    torch.cuda.synchronize()
+    part = partial[: blocks * 2 * co].view(blocks, 2, co).sum(0)
+    yf = y.float()
+    ref_s, ref_ss = yf.sum((0, 2, 3)), (yf * yf).sum((0, 2, 3))
+    assert torch.allclose(part[0], ref_s, rtol=1e-3, atol=1e-2), (part[0] - ref_s).abs().max()
+    assert torch.allclose(part[1], ref_ss, rtol=1e-3, atol=1e-2), (part[1] - ref_ss).abs().max()
+    assert _rel(y, conv.ref_fprop(x.float(), w.float(), s, p)) < 1e-2

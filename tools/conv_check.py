@@ -55,7 +55,11 @@ def main():
         dy = torch.randn(N, co, Ho, Ho, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         xf, wf, dyf = x.float(), w.float(), dy.float()
         try:
-            if a.kind == "fprop":
+            if a.kind == "fprop_stats":
+                from pytorch_distributed_tutorials_b200.ops import native
+                got = conv.conv_fprop_stats(x, w, s, p, native.bn_partial(dev))[0].float()
+                ref = conv.ref_fprop(xf, wf, s, p)
+            elif a.kind == "fprop":
                 got = conv.conv_fprop(x, w, s, p).float()
                 ref = conv.ref_fprop(xf, wf, s, p)
             elif a.kind == "dgrad":
@@ -73,7 +77,10 @@ def main():
             bad += (not ok)
             ms = ""
             if a.time and ok:
+                from pytorch_distributed_tutorials_b200.ops import native
+                part = native.bn_partial(dev)
                 fn = {"fprop": lambda: conv.conv_fprop(x, w, s, p),
+                      "fprop_stats": lambda: conv.conv_fprop_stats(x, w, s, p, part),
                       "dgrad": lambda: conv.conv_dgrad(dy, w, x.shape, s, p),
                       "wgrad": lambda: conv.conv_wgrad(x, dy, w.shape, s, p)}[a.kind]
                 for _ in range(3):
