@@ -218,12 +218,14 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 
 // ------------------------------------------------------------------------------------------------ backward
 // dz' = (dz_a [+ dz_b]) * (z > 0 if RELU).  Accumulates sum(dz') and sum(dz' * (y - mean)) per channel.
-template <bool RELU, bool TWO>
+// GOUT: dz' (rounded to bf16, which is what the sums then use) is also written out - it is the gradient of the
+// residual branch, and the apply pass then reads that one tensor instead of dz_a, dz_b and the mask again.
+template <bool RELU, bool TWO, bool GOUT>
 __global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
     bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
                          const __nv_bfloat16* __restrict__ z, const unsigned char* __restrict__ mask,
                          const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, float* partial,
-                         long long M, int C, long long rows_per_blk) {
+                         __nv_bfloat16* __restrict__ gout, long long M, int C, long long rows_per_blk) {
   extern __shared__ float smem[];
   const int C8 = C >> 3, RP = kBnThreads / C8;
   const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
@@ -252,6 +254,11 @@ __global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
 #pragma unroll
           for (int j = 0; j < 8; ++j) g.v[j] = zz.v[j] > 0.f ? g.v[j] : 0.f;
         }
+      }
+      if (GOUT) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g.v[j] = __bfloat162float(__float2bfloat16(g.v[j]));
+        store_bf16x8(gout + off, g);
       }
       Vec8 yy = load_bf16x8(y + off);
 #pragma unroll
@@ -475,7 +482,12 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
                       *zz = (const __nv_bfloat16*)z, *yy = (const __nv_bfloat16*)y;
   const bool dzb = dz_b != nullptr;
   const unsigned char* mk = (const unsigned char*)relu_mask;
-#define RED(R, T, ...) bn_bwd_reduce_kernel<R, T><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, M, C, rpb)
+  __nv_bfloat16 *dyp = (__nv_bfloat16*)dy, *drp = (__nv_bfloat16*)dres;
+#define RED(R, T, ...)                                                                                              \
+  do {                                                                                                              \
+    if (dres) bn_bwd_reduce_kernel<R, T, true><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb); \
+    else bn_bwd_reduce_kernel<R, T, false><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb);     \
+  } while (0)
   B2_BWD_DISPATCH(RED, 0);
 #undef RED
   XgpuCtx ctx = xgpu_from_c(xg);
@@ -483,12 +495,13 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
                                                           dbeta, accumulate, coef, ctx, xg_slot);
   const long long nvec = M * (C / 8);
   const int grid = stream_grid(nvec);
-  __nv_bfloat16 *dyp = (__nv_bfloat16*)dy, *drp = (__nv_bfloat16*)dres;
-#define APP(R, T, ...)                                                                                       \
-  do {                                                                                                       \
-    if (dres) bn_bwd_apply_kernel<R, T, true><<<grid, 256, 0, st>>>(a, b, zz, mk, yy, coef, dyp, drp, nvec, C / 8); \
-    else bn_bwd_apply_kernel<R, T, false><<<grid, 256, 0, st>>>(a, b, zz, mk, yy, coef, dyp, drp, nvec, C / 8);     \
-  } while (0)
+  if (dres) {
+    // the reduce pass has already produced dz' (= dres): dy = k1*dres + k2*y + k3
+    bn_bwd_apply_kernel<false, false, false><<<grid, 256, 0, st>>>(drp, nullptr, nullptr, nullptr, yy, coef, dyp,
+                                                                   nullptr, nvec, C / 8);
+    return cudaGetLastError();
+  }
+#define APP(R, T, ...) bn_bwd_apply_kernel<R, T, false><<<grid, 256, 0, st>>>(a, b, zz, mk, yy, coef, dyp, nullptr, nvec, C / 8)
   B2_BWD_DISPATCH(APP, 0);
 #undef APP
   return cudaGetLastError();

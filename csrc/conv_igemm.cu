@@ -49,6 +49,8 @@ struct ConvParams {
   // fprop (v2): per-CTA partial BatchNorm statistics of the bf16 output, [gridDim][2][Ncols] fp32 (sum, sum of
   // squares), accumulated tile by tile in a fixed order -> deterministic. nullptr = not requested.
   float* stats;
+  int panels;  // v2, MN-major operands fetched as one multi-panel TMA box: bit 0 = A (wgrad), bit 1 = B (dgrad/wgrad)
+  int dbg;  // timing experiments only (b2_conv_set_debug): 1 = skip the TMA loads once the ring is primed, 2 = skip the MMAs
 };
 
 constexpr int BM = 128;
@@ -423,6 +425,8 @@ static int pick_bn(int ncols, int force) {
 }
 
 static int g_force_bn = 0;
+static int g_dbg = 0;
+static int g_panels = 1;  // v2: fetch MN-major operands as one multi-panel TMA box (b2_conv_set_panels)
 static int g_act_mode = -1;  // -1 auto, else force ACT_GATHER / ACT_IM2COL for k>1 or strided convs
 
 template <int KIND>
@@ -564,6 +568,10 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
           const int s = g % C::kStages;
           const uint32_t ph = (g / C::kStages) & 1;
           mbar_wait(&empty[s], ph ^ 1);
+          if ((p.dbg & 1) && g >= (uint32_t)C::kStages) {
+            mbar_arrive(&full[s]);
+            continue;
+          }
           uint8_t* sA = smem + s * C::kStageBytes;
           uint8_t* sB = sA + kABytes;
           uint32_t txB = kBBytes;
@@ -594,13 +602,21 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
               tma_load_2d(sA, &tmA, &full[s], kb * BK, it.m0);
             }
             if (doB) {
+              if (p.panels & 2) {
+                tma_load_3d(sB, &tmB, &full[s], 0, cob * 64, (tapidx * p.tapC + it.n0) >> 6);
+              } else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(sB + j * 8192, &tmB, &full[s], tapidx * p.tapC + it.n0 + 64 * j, cob * 64);
+                for (int j = 0; j < BN / 64; ++j)
+                  tma_load_2d(sB + j * 8192, &tmB, &full[s], tapidx * p.tapC + it.n0 + 64 * j, cob * 64);
+              }
             }
           } else if (doA) {
+            if (p.panels & 1) {
+              tma_load_3d(sA, &tmA, &full[s], 0, kb * BK, it.m0 >> 6);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
+              for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
+            }
           } else {
             if (IM2COL) {
               int n, h, w;
@@ -618,6 +634,8 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
                 for (int j = 0; j < BN / 64; ++j)
                   tma_load_im2col(sB + j * 8192, &tmB, &full[s], it.n0 + 64 * j, bw, bh, n, (uint16_t)kw, (uint16_t)kh);
               }
+            } else if (p.panels & 2) {
+              tma_load_3d(sB, &tmB, &full[s], 0, kb * BK, it.n0 >> 6);
             } else {
 #pragma unroll
               for (int j = 0; j < BN / 64; ++j)
@@ -653,7 +671,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
                                      : make_smem_desc_sw128(aBase + k * 32, 16, 1024);
             const uint64_t db = kBmn ? make_smem_desc_sw128(bBase + k * 2048, 8192, 1024)
                                      : make_smem_desc_sw128(bBase + k * 32, 16, 1024);
-            umma_bf16(d_tmem, da, db, idesc, (i | k) != 0);
+            if (!(p.dbg & 2)) umma_bf16(d_tmem, da, db, idesc, (i | k) != 0);
           }
           umma_commit(&empty[s]);
         }
@@ -1171,8 +1189,10 @@ static int num_sms() {
 }
 
 template <int KIND, int AMODE, int BN>
-static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int items,
+static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p_in, int items,
                            cudaStream_t st) {
+  ConvParams p = p_in;
+  p.dbg = g_dbg;
   CUtensorMap tmC = tmB;  // wgrad and class-strided dgrad never dereference it
   if (KIND != WGRAD && p.cls == 1) {
     int e = make_tmap_2d_bf16(&tmC, p.out, (uint64_t)p.Ncols, (uint64_t)p.M, 64, 128);
@@ -1251,6 +1271,8 @@ using namespace b2;
 
 extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
 extern "C" void b2_conv_set_act_mode(int mode) { g_act_mode = mode; }
+extern "C" void b2_conv_set_debug(int bits) { g_dbg = bits; }
+extern "C" void b2_conv_set_panels(int on) { g_panels = on; }
 
 extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
 
@@ -1330,7 +1352,12 @@ static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int 
                             int KW, int stride, int pad, int Ho, int Wo, int bn, cudaStream_t st) {
   CUtensorMap tmB;
   int e;
-  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) return e;
+  const bool panelsB = g_panels && g_impl == 2;   // every parity class goes through the persistent kernel
+  if (panelsB) {
+    if ((e = make_tmap_panels_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, bn / 64))) return e;
+  } else if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) {
+    return e;
+  }
   const int cpb = (Cout + 63) / 64;
   bool need_zero = false;
   for (int ph = 0; ph < stride; ++ph)
@@ -1362,6 +1389,7 @@ static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int 
       p.im2col_pad_h = -lower_h; p.im2col_pad_w = -lower_w;
       p.kh0 = kh0; p.kw0 = kw0; p.kstep = stride; p.nth = nth; p.ntw = ntw;
       p.cls = stride; p.ph = ph; p.pw = pw; p.outH = H; p.outW = W; p.taps = KH * KW;
+      p.panels = panelsB ? 2 : 0;
       p.n_tiles = Cin / bn; p.m_tiles = (p.M + BM - 1) / BM;
       cudaError_t ce;
       if (use_pairs(bn, p.M)) {
@@ -1396,8 +1424,14 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) {
     return e;
   }
-  if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) return e;
+  const bool panelsB = g_panels && g_impl == 2 && mode != ACT_GATHER;   // the persistent (non-pair) kernel runs
+  if (panelsB) {
+    if ((e = make_tmap_panels_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, bn / 64))) return e;
+  } else if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) {
+    return e;
+  }
   ConvParams p{};
+  p.panels = panelsB ? 2 : 0;
   p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
   p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cin; p.Kblocks = KH * KW * cpb; p.cpb = cpb; p.tapC = Cin;
@@ -1450,14 +1484,24 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const int per = (kblocks + splits - 1) / splits;
   CUtensorMap tmA, tmB;
   int e;
-  if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, 64))) return e;
+  const bool v2 = g_impl == 2 && mode != ACT_GATHER;   // the persistent (non-pair) kernel runs
+  const bool panelsA = g_panels && v2 && Cout % 64 == 0;
+  const bool panelsB = g_panels && v2 && mode != ACT_IM2COL;
+  if (panelsA) {
+    if ((e = make_tmap_panels_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, BM / 64))) return e;
+  } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, 64))) {
+    return e;
+  }
   if (mode == ACT_IM2COL) {
     if ((e = make_tmap_im2col_bf16(&tmB, x, N, H, W, Cin, -pad, -pad, pad - (KW - 1), pad - (KH - 1), 64, 64, stride)))
       return e;
+  } else if (panelsB) {
+    if ((e = make_tmap_panels_bf16(&tmB, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, bn / 64))) return e;
   } else if ((e = make_tmap_2d_bf16(&tmB, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 64))) {
     return e;
   }
   ConvParams p{};
+  p.panels = (panelsA ? 1 : 0) | (panelsB ? 2 : 0);
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
   p.rowH = Ho; p.rowW = Wo; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad; p.im2col_pad = pad;
   p.im2col_pad_h = pad; p.im2col_pad_w = pad; p.cls = 1; p.taps = taps;

@@ -22,6 +22,23 @@ static EncodeTiledFn resolve_encode() {
   return fn;
 }
 
+int make_tmap_panels_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint32_t box_outer,
+                          uint32_t panels) {
+  EncodeTiledFn enc = resolve_encode();
+  if (!enc) return (int)cudaErrorNotSupported;
+  if (inner % 64) return (int)cudaErrorInvalidValue;
+  // dim0: 64 elements inside a panel, dim1: matrix rows, dim2: panel index (stride 128 bytes). The box is written to
+  // shared memory dim0-fastest, then dim1, then dim2: one [box_outer x 128 B] swizzled panel per 64 columns.
+  cuuint64_t dims[3] = {64, outer, inner / 64};
+  cuuint64_t strides[2] = {inner * 2, 128};
+  cuuint32_t box[3] = {64, box_outer, panels};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return (int)r;
+}
+
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint32_t box_inner,
                       uint32_t box_outer) {
   EncodeTiledFn enc = resolve_encode();

@@ -46,6 +46,10 @@ int b2_conv_fprop(const void* x, const void* w, const float* bias /*nullable, fp
 int b2_conv_fprop_stats(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                         int stride, int pad, float* stats, int* stats_blocks, void* stream);
 void b2_conv_set_fuse_stats(int on);
+/* timing experiments only (results are wrong): 1 = skip operand loads once the smem ring is primed, 2 = skip MMAs */
+void b2_conv_set_debug(int bits);
+/* 1 (default): MN-major operands (dgrad weights, wgrad dy / 1x1 x) are fetched as one multi-panel TMA box */
+void b2_conv_set_panels(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.

@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--time", action="store_true")
     ap.add_argument("--act-mode", type=int, default=-1)
     ap.add_argument("--impl", type=int, default=2)
+    ap.add_argument("--debug-bits", type=int, default=0, help="timing experiments: 1 skip loads, 2 skip MMAs")
     ap.add_argument("--shape", default=None, help="ci,co,k,s,p,H: run only this shape")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -42,6 +43,7 @@ def main():
     _lib.lib().b2_conv_set_tile_n(a.bn)
     _lib.lib().b2_conv_set_act_mode(a.act_mode)
     _lib.lib().b2_conv_set_impl(a.impl)
+    _lib.lib().b2_conv_set_debug(a.debug_bits)
     shapes = SHAPES[: a.limit] if a.limit else SHAPES
     if a.shape:
         shapes = [tuple(int(v) for v in a.shape.split(','))]
@@ -76,7 +78,7 @@ def main():
             ok = rel < 2e-2
             bad += (not ok)
             ms = ""
-            if a.time and ok:
+            if a.time and (ok or a.debug_bits):
                 from pytorch_distributed_tutorials_b200.ops import native
                 part = native.bn_partial(dev)
                 fn = {"fprop": lambda: conv.conv_fprop(x, w, s, p),
