@@ -132,6 +132,20 @@ int b2_sgd_step(float* p, const float* g, float* buf, void* shadow_bf16, long lo
                 float weight_decay, float grad_scale, int first_step, void* stream);
 int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
 int b2_stem_im2col(const void* x_nchw, int x_is_bf16, void* A, int N, int H, int W, void* stream);
+/* Direct stem (csrc/stem.cu): the 7x7/2 convolution on the tensor cores straight from a zero-padded NHWC4 bf16 copy
+ * of the batch (overlapping-window TMA boxes), no im2col matrix in memory. b2_stem_supported: output width <= 112.
+ * xp holds b2_stem_padded_elems(N,H,W) bf16, written entirely (padding included) by b2_stem_pack_input;
+ * wp is bf16 [64][224]; stats / stats_blocks as in b2_conv_fprop_stats (2 rows per CTA);
+ * workspace holds b2_stem_wgrad_workspace_floats() floats; dw is fp32 OHWI [64][7][7][3]. */
+int b2_stem_supported(int H, int W);
+long long b2_stem_padded_elems(int N, int H, int W);
+int b2_stem_pack_input(const void* x_nchw, int x_is_bf16, void* xp, int N, int H, int W, void* stream);
+int b2_stem_pack_weight(const float* w_ohwi, void* wp, void* stream);
+int b2_stem_fprop(const void* xp, const void* wp, void* y, int N, int H, int W, float* stats, int* stats_blocks,
+                  void* stream);
+long long b2_stem_wgrad_workspace_floats(void);
+int b2_stem_wgrad(const void* xp, const void* dy, float* dw_ohwi, float* workspace, int N, int H, int W,
+                  int accumulate, void* stream);
 int b2_stem_pack_w(const float* w_ohwi, void* wp_bf16, int Cout, void* stream);
 int b2_stem_unpack_dw(const float* dwp, float* dw_ohwi, int Cout, int accumulate, void* stream);
 int b2_nchw_to_nhwc_bf16(const void* x, int x_is_bf16, void* y, int N, int C, int HW, void* stream);

@@ -210,6 +210,9 @@ class ResNetEngine:
         self.local_versions = {}
         self.stem_wp = torch.zeros(64, 192, dtype=torch.bfloat16, device=self.device)
         self.stem_dwp = torch.zeros(64, 192, dtype=torch.float32, device=self.device)
+        self.stem_wp_direct = torch.zeros(64, 224, dtype=torch.bfloat16, device=self.device)
+        # direct stem (no im2col matrix); B200DDP_STEM=im2col selects the materialised-im2col GEMM path instead
+        self.stem_direct = os.environ.get("B200DDP_STEM", "direct") != "im2col"
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
         self.xg_slot = 0           # float offset of the statistics exchange area inside the symmetric window
@@ -284,18 +287,28 @@ class ResNetEngine:
     def _stem(self, x, training, tape):
         m = self.model
         xin = x if x.dtype in (torch.float32, torch.bfloat16) else x.float()
-        a, ho, wo = native.stem_im2col(xin.contiguous())
+        xin = xin.contiguous()
         w_ohwi = m.conv1.weight.detach().permute(0, 2, 3, 1)   # a free view when the weight is stored OHWI
         if not w_ohwi.is_contiguous():
             w_ohwi = w_ohwi.contiguous()
-        native.stem_pack_w(w_ohwi, self.stem_wp)                # fp32 OHWI [64,147] -> bf16 [64,192]
+        n, _, h, w = x.shape
+        want_stats = training or m.bn1.running_mean is None
         blocks = 0
-        if training or m.bn1.running_mean is None:
-            y2d, blocks = convops.gemm_nt_stats(a, self.stem_wp, native.bn_partial(self.device))
+        if self.stem_direct and native.stem_supported(h, w):
+            # tensor-core convolution straight from a padded NHWC4 copy of the batch (csrc/stem.cu)
+            xp = native.stem_pack_input(xin)
+            native.stem_pack_weight(w_ohwi, self.stem_wp_direct)
+            y, blocks = native.stem_fprop(xp, self.stem_wp_direct, n, h, w,
+                                          native.bn_partial(self.device) if want_stats else None)
+            a = ("direct", xp, (n, h, w))
         else:
-            y2d = convops.gemm_nt(a, self.stem_wp)
-        n = x.shape[0]
-        y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
+            a, ho, wo = native.stem_im2col(xin)
+            native.stem_pack_w(w_ohwi, self.stem_wp)            # fp32 OHWI [64,147] -> bf16 [64,192]
+            if want_stats:
+                y2d, blocks = convops.gemm_nt_stats(a, self.stem_wp, native.bn_partial(self.device))
+            else:
+                y2d = convops.gemm_nt(a, self.stem_wp)
+            y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
         mask = self._new_mask(y) if tape is not None else None
         z = self._bn_apply(y, m.bn1, True, None, training, mask, blocks)
         if tape is not None:
@@ -357,6 +370,11 @@ class ResNetEngine:
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight
+        if isinstance(rec.stem_a, tuple):
+            _, xp, (n, h, wd) = rec.stem_a
+            g = self._deliver(w, lambda out, acc: native.stem_wgrad(xp, dy, out, n, h, wd, acc))
+            grads[id(w)] = g
+            return None, dres
         if rec.stem_a is not None:
             dy2d = dy.permute(0, 2, 3, 1).reshape(-1, 64)
             convops.gemm_tn(dy2d, rec.stem_a, self.stem_dwp)

@@ -201,6 +201,52 @@ def stem_unpack_dw(dwp, dw, accumulate):
     count_launch()
 
 
+def stem_supported(h, w):
+    return bool(_lib.lib().b2_stem_supported(int(h), int(w)))
+
+
+def stem_pack_input(x):
+    """[N,3,H,W] fp32/bf16 NCHW -> zero-padded NHWC4 bf16 image (flat) for the direct stem kernels."""
+    n, c, h, w = x.shape
+    assert c == 3 and x.is_contiguous()
+    lib = _lib.lib()
+    lib.b2_stem_padded_elems.restype = ctypes.c_longlong
+    xp = torch.empty(lib.b2_stem_padded_elems(n, h, w), dtype=torch.bfloat16, device=x.device)
+    check(lib.b2_stem_pack_input(ptr(x), int(x.dtype == torch.bfloat16), ptr(xp), n, h, w, stream_ptr()),
+          "b2_stem_pack_input")
+    count_launch()
+    return xp
+
+
+def stem_pack_weight(w_ohwi_fp32, out):
+    """fp32 OHWI [64,7,7,3] -> bf16 [64,224] (7 filter rows x 8 columns x 4 channels, zero padded)."""
+    check(_lib.lib().b2_stem_pack_weight(ptr(w_ohwi_fp32), ptr(out), stream_ptr()), "b2_stem_pack_weight")
+    count_launch()
+    return out
+
+
+def stem_fprop(xp, wp, n, h, w, partial=None):
+    """7x7/2 stem convolution from the padded image. Returns (y [N,64,Ho,Wo] channels_last bf16, stats blocks)."""
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, 64, ho, wo), dtype=torch.bfloat16, device=xp.device, memory_format=torch.channels_last)
+    blocks = ctypes.c_int(0)
+    check(_lib.lib().b2_stem_fprop(ptr(xp), ptr(wp), ptr(y), n, h, w, ptr(partial),
+                                   ctypes.byref(blocks) if partial is not None else None, stream_ptr()),
+          "b2_stem_fprop")
+    count_launch()
+    return y, blocks.value
+
+
+def stem_wgrad(xp, dy, dw, n, h, w, accumulate):
+    """dW (fp32 OHWI [64,7,7,3], written or accumulated) of the stem from the padded image and dy (NHWC bf16)."""
+    lib = _lib.lib()
+    lib.b2_stem_wgrad_workspace_floats.restype = ctypes.c_longlong
+    ws = scratch(xp.device, "stem_wgrad_ws", lib.b2_stem_wgrad_workspace_floats())
+    check(lib.b2_stem_wgrad(ptr(xp), ptr(dy), ptr(dw), ptr(ws), n, h, w, int(accumulate), stream_ptr()),
+          "b2_stem_wgrad")
+    count_launch(2)
+
+
 def nchw_to_nhwc_bf16(x):
     n, c, h, w = x.shape
     assert x.is_contiguous()

@@ -226,3 +226,38 @@ def test_conv_epilogue_bn_statistics(ci, co, k, s, p, H, N):
     assert torch.allclose(part[0], ref_s, rtol=1e-3, atol=1e-2), (part[0] - ref_s).abs().max()
     assert torch.allclose(part[1], ref_ss, rtol=1e-3, atol=1e-2), (part[1] - ref_ss).abs().max()
     assert _rel(y, conv.ref_fprop(x.float(), w.float(), s, p)) < 1e-2
+
+
+@pytest.mark.parametrize("N,H,W", [(4, 224, 224), (3, 32, 32), (2, 64, 96), (5, 57, 45)])
+def test_direct_stem_conv(N, H, W):
+    """7x7/2 stem straight from a padded NHWC4 image (overlapping-window TMA boxes): fprop, BN statistics, wgrad."""
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(11)
+    assert native.stem_supported(H, W)
+    x = torch.randn(N, 3, H, W, device=DEV)
+    w = torch.randn(64, 3, 7, 7, device=DEV) / 147 ** 0.5
+    w_ohwi = w.permute(0, 2, 3, 1).contiguous()
+    wp = torch.empty(64, 224, dtype=torch.bfloat16, device=DEV)
+    native.stem_pack_weight(w_ohwi, wp)
+    xp = native.stem_pack_input(x)
+    partial = native.bn_partial(torch.device(DEV))
+    partial.fill_(float("nan"))
+    y, blocks = native.stem_fprop(xp, wp, N, H, W, partial)
+    torch.cuda.synchronize()
+    xr, wr = x.to(torch.bfloat16).float(), w.to(torch.bfloat16).float()
+    ref = torch.nn.functional.conv2d(xr, wr, stride=2, padding=3)
+    assert y.shape == ref.shape
+    assert _rel(y, ref) < 1e-2
+    assert blocks > 0
+    part = partial[: blocks * 2 * 64].view(blocks, 2, 64).sum(0)
+    yf = y.float()
+    assert torch.allclose(part[0], yf.sum((0, 2, 3)), rtol=1e-3, atol=5e-2)
+    assert torch.allclose(part[1], (yf * yf).sum((0, 2, 3)), rtol=1e-3, atol=5e-2)
+    # weight gradient
+    dy = _bf(torch.randn_like(ref))
+    dw = torch.full((64, 7, 7, 3), float("nan"), device=DEV)
+    native.stem_wgrad(xp, dy, dw, N, H, W, False)
+    ref_dw = torch.nn.grad.conv2d_weight(xr, w.shape, dy.float(), stride=2, padding=3)
+    assert _rel(dw.permute(0, 3, 1, 2), ref_dw) < 5e-3
+    native.stem_wgrad(xp, dy, dw, N, H, W, True)
+    assert _rel(dw.permute(0, 3, 1, 2), 2 * ref_dw) < 5e-3
