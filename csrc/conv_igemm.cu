@@ -49,6 +49,10 @@ struct ConvParams {
   // fprop (v2): per-CTA partial BatchNorm statistics of the bf16 output, [gridDim][2][Ncols] fp32 (sum, sum of
   // squares), accumulated tile by tile in a fixed order -> deterministic. nullptr = not requested.
   float* stats;
+  // dgrad epilogue fusion (v2, TMA-store path): dx = relu_mask ? (acc + add) : 0 — the gradient fan-in of a residual
+  // fork and the ReLU backward of the tensor being differentiated, applied before the single bf16 rounding.
+  const __nv_bfloat16* add;     // [M][Ncols] bf16, optional
+  const unsigned char* amask;   // [M][Ncols/8] bits, optional (only with add)
   int panels;  // v2, MN-major operands fetched as one multi-panel TMA box: bit 0 = A (wgrad), bit 1 = B (dgrad/wgrad)
   int dbg;  // timing experiments only (b2_conv_set_debug): 1 = skip the TMA loads once the ring is primed, 2 = skip the MMAs
 };
@@ -800,9 +804,33 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
           if (it.n0 + pn * 64 >= p.Ncols) break;
           const uint32_t bsel = panel_seq & 1;
           uint8_t* buf = epi_smem + bsel * (BM * 128);
+          uint4 addv[4];
+          uint32_t mbits = 0xffffffffu;
+          const bool fuse_add = (KIND == DGRAD) && p.add != nullptr && ok;
+          if (KIND == DGRAD && fuse_add) {   // issued before the TMEM load so that the two latencies overlap
+            const int col0 = it.n0 + pn * 64 + eg * 32;
+            const __nv_bfloat16* ap = p.add + (size_t)m * p.Ncols + col0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) addv[q] = ld_nc_v4(ap + 8 * q);
+            if (p.amask)
+              mbits = __ldg(reinterpret_cast<const unsigned int*>(p.amask + (size_t)m * (p.Ncols >> 3) + (col0 >> 3)));
+          }
           uint32_t v[32];
           tmem_ld32(taddr + pn * 64 + eg * 32, v);
           tmem_ld_wait();
+          if (KIND == DGRAD && fuse_add) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t ww[4] = {addv[q].x, addv[q].y, addv[q].z, addv[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float lo = __uint_as_float(ww[e] << 16), hi = __uint_as_float(ww[e] & 0xffff0000u);
+                const int j = 8 * q + 2 * e;
+                v[j] = ((mbits >> j) & 1u) ? __float_as_uint(__uint_as_float(v[j]) + lo) : 0u;
+                v[j + 1] = ((mbits >> (j + 1)) & 1u) ? __float_as_uint(__uint_as_float(v[j + 1]) + hi) : 0u;
+              }
+            }
+          }
           if (p.bias) {
             const int col = it.n0 + pn * 64 + eg * 32;
 #pragma unroll
@@ -1404,8 +1432,28 @@ static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int 
   return 0;
 }
 
+static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                           int KW, int stride, int pad, const void* add, const void* mask, void* stream);
+
 extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
                              int KW, int stride, int pad, void* stream) {
+  return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, nullptr, nullptr, stream);
+}
+
+// dx = mask ? (dgrad + add) : 0 in the epilogue (add: bf16 [N,H,W,Cin]; mask: 1 bit per element, optional).
+// Returns -1 (nothing launched) when the active kernel variant cannot fuse it: the caller then runs the plain dgrad
+// and its own add / mask pass.
+extern "C" int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                   int KH, int KW, int stride, int pad, const void* add, const void* mask,
+                                   void* stream) {
+  if (!add) return cudaErrorInvalidValue;
+  const bool v2_tma_epilogue = g_impl == 2 && stride == 1 && pick_mode(DGRAD, KH, KW, stride, pad) != ACT_GATHER;
+  if (!v2_tma_epilogue) return -1;
+  return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, add, mask, stream);
+}
+
+static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                           int KW, int stride, int pad, const void* add, const void* mask, void* stream) {
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * H * W;
@@ -1432,6 +1480,8 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   }
   ConvParams p{};
   p.panels = panelsB ? 2 : 0;
+  p.add = (const __nv_bfloat16*)add;
+  p.amask = (const unsigned char*)mask;
   p.src = (const __nv_bfloat16*)dy; p.srcH = Ho; p.srcW = Wo; p.srcC = Cout;
   p.rowH = H; p.rowW = W; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.M = M; p.Ncols = Cin; p.Kblocks = KH * KW * cpb; p.cpb = cpb; p.tapC = Cin;

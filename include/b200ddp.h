@@ -52,6 +52,11 @@ void b2_conv_set_debug(int bits);
 void b2_conv_set_panels(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
+/* dgrad with the gradient fan-in and the ReLU backward fused into the epilogue: dx = mask ? (dgrad + add) : 0
+ * (add: bf16 NHWC like dx; mask: 1 bit per element as written by b2_bn_fwd_train, nullable). Returns -1 without
+ * launching anything when the active kernel variant cannot fuse it. */
+int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                        int KW, int stride, int pad, const void* add, const void* mask, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.
  * accumulate != 0 adds into dw (gradient accumulation / no_sync), otherwise dw is overwritten. */
 int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N, int H, int W,

@@ -142,10 +142,12 @@ class ResNet(nn.Module):
                 us = blk.units()
                 last_conv, last_bn = us[-1]
                 order += [last_bn.weight, last_bn.bias, last_conv.weight]
-                for c, b in reversed(us[:-1]):
+                for c, b in reversed(us[1:-1]):
                     order += [b.weight, b.bias, c.weight]
                 if blk.downsample is not None:
                     order += [blk.downsample[1].weight, blk.downsample[1].bias, blk.downsample[0].weight]
+                c, b = us[0]     # the first conv's dgrad absorbs the skip-path gradient, so it runs last
+                order += [b.weight, b.bias, c.weight]
         order += [self.bn1.weight, self.bn1.bias, self.conv1.weight]
         return order
 
@@ -213,6 +215,10 @@ class ResNetEngine:
         self.stem_wp_direct = torch.zeros(64, 224, dtype=torch.bfloat16, device=self.device)
         # direct stem (no im2col matrix); B200DDP_STEM=im2col selects the materialised-im2col GEMM path instead
         self.stem_direct = os.environ.get("B200DDP_STEM", "direct") != "im2col"
+        # fuse the residual fan-in add + ReLU backward into the first conv's dgrad epilogue. Off by default: the
+        # epilogue's row-per-thread reads of the skip gradient cost more than the BatchNorm-backward bytes they save
+        # (measured: R50 bs256 dgrad +3.0 ms vs BN reduce -1.2 ms).
+        self.fuse_fanin = os.environ.get("B200DDP_FUSE_FANIN", "0") == "1"
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
         self.xg_slot = 0           # float offset of the statistics exchange area inside the symmetric window
@@ -358,15 +364,25 @@ class ResNetEngine:
         writer(out, False)
         return out
 
-    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads):
+    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, dx_add=None, dx_mask=None):
+        """Backward of one conv+BN(+ReLU) unit. ``pre_masked``: dz_a already is the complete, ReLU-masked gradient
+        of this unit's output (produced by a fused dgrad epilogue), so it doubles as the residual-branch gradient.
+        ``dx_add`` / ``dx_mask``: fan-in gradient (and the ReLU mask of this unit's input) to fuse into the dgrad
+        epilogue; the returned flag says whether that happened."""
         conv, bn = rec.conv, rec.bn
         st = self._bn(bn)
         # BN backward needs dgamma/dbeta destinations up front (the finalize kernel writes them).
         dg_slot = self._slot(bn.weight)
         db_slot = self._slot(bn.bias)
-        dy, dres = native.bn_bwd(dz_a, dz_b, None, rec.y, bn.weight, st.mean, st.invstd,
-                                 dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
-                                 self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
+        if pre_masked:
+            dy, _ = native.bn_bwd(dz_a, None, None, rec.y, bn.weight, st.mean, st.invstd,
+                                  dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], False, st.coef, False,
+                                  self._sync_bn_ctx(bn), self.xg_slot, None)
+            dres = dz_a
+        else:
+            dy, dres = native.bn_bwd(dz_a, dz_b, None, rec.y, bn.weight, st.mean, st.invstd,
+                                     dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
+                                     self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight
@@ -384,9 +400,16 @@ class ResNetEngine:
         s, pd = conv.stride[0], conv.padding[0]
         # dgrad first: delivering the weight gradient may complete a bucket, and the fused all-reduce + SGD kernel
         # that this triggers rewrites the bucket's weights — every reader of the old weights must already be queued
-        dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd) if need_dx else None
+        dx, fused = None, False
+        if need_dx and dx_add is not None:
+            dx = convops.conv_dgrad_fused(dy, self._w16(w), rec.x.shape, s, pd, dx_add, dx_mask)
+            fused = dx is not None
+        if need_dx and dx is None:
+            dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd)
         g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
         grads[id(w)] = g
+        if dx_add is not None:
+            return dx, fused
         return dx, dres
 
     def _slot(self, p):
@@ -416,19 +439,30 @@ class ResNetEngine:
         grads[id(m.fc.bias)] = self._deliver(m.fc.bias, lambda out, acc: native.colsum_bf16(dl, out, acc))
         grads[id(m.fc.weight)] = self._deliver(m.fc.weight, lambda out, acc: convops.gemm_tn(dl, pooled, out, acc))
         da, db = native.avgpool_bwd(dpooled, feat_shape), None
-        for blk, bt in reversed(block_tapes):
+        rev = list(reversed(block_tapes))
+        pre_masked = False
+        for i, (blk, bt) in enumerate(rev):
             n_main = len(blk.units())
             recs_main = bt[:n_main - 1]
             rec_ds = bt[n_main - 1] if blk.downsample is not None else None
             rec_last = bt[-1]
-            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads)
-            for rec in reversed(recs_main):
+            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_masked)
+            for rec in reversed(recs_main[1:]):
                 d, _ = self._unit_bwd(rec, d, None, True, False, grads)
+            # gradient of the block input = dgrad(first conv) + skip-path gradient, masked by the ReLU that produced
+            # the input (the previous block's output ReLU): both fused into the first conv's dgrad epilogue
+            skip = dres
             if rec_ds is not None:
-                dds, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
-                da, db = d, dds
+                skip, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
+            prev_mask = rev[i + 1][1][-1].mask if i + 1 < len(rev) else None
+            if self.fuse_fanin:
+                d, fused = self._unit_bwd(recs_main[0], d, None, True, False, grads, dx_add=skip, dx_mask=prev_mask)
             else:
-                da, db = d, dres
+                (d, _), fused = self._unit_bwd(recs_main[0], d, None, True, False, grads), False
+            if fused:
+                da, db, pre_masked = d, None, prev_mask is not None
+            else:
+                da, db, pre_masked = d, skip, False
         dz = native.maxpool_bwd(pool_idx, stem_shape, da, db)
         self._unit_bwd(tape[0], dz, None, False, False, grads)
         return grads

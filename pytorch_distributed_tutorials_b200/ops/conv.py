@@ -116,6 +116,22 @@ def gemm_nt_stats(a, w, partial):
     return y, blocks.value
 
 
+def conv_dgrad_fused(dy, w, x_shape, stride, pad, add, mask=None):
+    """dx = mask ? (dgrad + add) : 0 with the add / ReLU-mask applied in the dgrad epilogue. Returns None when the
+    active kernel variant cannot fuse it (the caller then falls back to conv_dgrad plus its own fan-in)."""
+    N, Cin, H, W = x_shape
+    Cout, _, KH, KW = w.shape
+    assert _is_cl(dy) and _is_cl(w) and _is_cl(add) and tuple(add.shape) == tuple(x_shape)
+    dx = torch.empty((N, Cin, H, W), dtype=torch.bfloat16, device=dy.device, memory_format=torch.channels_last)
+    e = _lib.lib().b2_conv_dgrad_fused(_lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), N, H, W, Cin, Cout, KH, KW, stride,
+                                       pad, _lib.ptr(add), _lib.ptr(mask), _lib.stream_ptr())
+    if e == -1:
+        return None
+    _lib.check(e, "b2_conv_dgrad_fused")
+    _lib.count_launch()
+    return dx
+
+
 def conv_dgrad(dy, w, x_shape, stride, pad):
     N, Cin, H, W = x_shape
     Cout, _, KH, KW = w.shape

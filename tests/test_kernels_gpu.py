@@ -261,3 +261,24 @@ def test_direct_stem_conv(N, H, W):
     assert _rel(dw.permute(0, 3, 1, 2), ref_dw) < 5e-3
     native.stem_wgrad(xp, dy, dw, N, H, W, True)
     assert _rel(dw.permute(0, 3, 1, 2), 2 * ref_dw) < 5e-3
+
+
+@pytest.mark.parametrize("ci,co,k,p,H,N", [(256, 64, 1, 0, 28, 4), (64, 64, 3, 1, 14, 3), (512, 128, 1, 0, 7, 5)])
+def test_conv_dgrad_epilogue_fan_in_and_relu_mask(ci, co, k, p, H, N):
+    """dx = mask ? (dgrad + add) : 0 applied in the dgrad epilogue (residual fan-in + ReLU backward)."""
+    from pytorch_distributed_tutorials_b200.ops import conv
+    torch.manual_seed(5)
+    w = _bf(torch.randn(co, ci, k, k, device=DEV) / (ci * k * k) ** 0.5)
+    dy = _bf(torch.randn(N, co, H, H, device=DEV))
+    add = _bf(torch.randn(N, ci, H, H, device=DEV))
+    keep = torch.rand(N, H, H, ci, device=DEV) > 0.4                     # NHWC, as the mask is laid out
+    bits = (keep.view(N, H, H, ci // 8, 8).to(torch.uint8) << torch.arange(8, device=DEV, dtype=torch.uint8)).sum(
+        -1).to(torch.uint8)
+    got = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, bits)
+    assert got is not None
+    ref = conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p) + add.float()
+    ref = torch.where(keep.permute(0, 3, 1, 2), ref, torch.zeros_like(ref))
+    assert _rel(got, ref) < 1e-2
+    assert (got.float()[~keep.permute(0, 3, 1, 2)] == 0).all()
+    got2 = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, None)
+    assert _rel(got2, conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p) + add.float()) < 1e-2
