@@ -67,27 +67,38 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
 }
 
 // dx[h,w] = sum over the (<=4) windows containing (h,w) of (dy_a [+ dy_b])[window] * [winner(window) == (h,w)].
+// One thread per 2x2 input quad (rows 2a, 2a+1; columns 2b, 2b+1) and 8 channels: exactly the windows
+// {a, a+1} x {b, b+1} touch the quad, so each window's (index, gradient) vectors are loaded once per quad instead
+// of once per pixel.
 template <bool TWO>
 __global__ void __launch_bounds__(256)
     maxpool_bwd_kernel(const unsigned char* __restrict__ idx, const __nv_bfloat16* __restrict__ dya,
                        const __nv_bfloat16* __restrict__ dyb, __nv_bfloat16* __restrict__ dx, int N, int H, int W,
                        int C8, int Ho, int Wo) {
-  const long long total = (long long)N * H * W * C8;
+  const int Hq = (H + 1) >> 1, Wq = (W + 1) >> 1;
+  const long long total = (long long)N * Hq * Wq * C8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int cv = (int)(i % C8);
-    long long pix = i / C8;
-    const int w = (int)(pix % W); pix /= W;
-    const int h = (int)(pix % H);
-    const int n = (int)(pix / H);
-    float acc[8];
+    long long q = i / C8;
+    const int b = (int)(q % Wq); q /= Wq;
+    const int a = (int)(q % Hq);
+    const int n = (int)(q / Hq);
+    float acc[2][2][8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    const int oh0 = h >> 1, oh1 = min(Ho - 1, (h + 1) >> 1);
-    const int ow0 = w >> 1, ow1 = min(Wo - 1, (w + 1) >> 1);
-    for (int oh = oh0; oh <= oh1; ++oh) {
-      for (int ow = ow0; ow <= ow1; ++ow) {
-        const unsigned code = (unsigned)((h - (oh * 2 - 1)) * 3 + (w - (ow * 2 - 1)));
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[r][c][j] = 0.f;
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh) {
+      const int oh = a + dh;
+      if (oh >= Ho) continue;
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const int ow = b + dw;
+        if (ow >= Wo) continue;
         const long long o = (((long long)(n * Ho + oh) * Wo + ow) * C8 + cv) * 8;
         const uint2 id = *reinterpret_cast<const uint2*>(idx + o);
         float g[8];
@@ -98,14 +109,36 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] += g2[j];
         }
+        // window (oh, ow) covers rows 2oh-1..2oh+1: quad row r (h = 2a + r) is tap kh = h - (2oh - 1) = r + 1 - 2dh
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          acc[j] += (((id.x >> (8 * j)) & 0xFFu) == code) ? g[j] : 0.f;
-          acc[4 + j] += (((id.y >> (8 * j)) & 0xFFu) == code) ? g[4 + j] : 0.f;
+        for (int r = 0; r < 2; ++r) {
+          const int kh = r + 1 - 2 * dh;
+          if (kh < 0 || kh > 2) continue;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const int kw = c + 1 - 2 * dw;
+            if (kw < 0 || kw > 2) continue;
+            const unsigned code = (unsigned)(kh * 3 + kw);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              acc[r][c][j] += (((id.x >> (8 * j)) & 0xFFu) == code) ? g[j] : 0.f;
+              acc[r][c][4 + j] += (((id.y >> (8 * j)) & 0xFFu) == code) ? g[4 + j] : 0.f;
+            }
+          }
         }
       }
     }
-    *reinterpret_cast<uint4*>(dx + i * 8) = pack8(acc);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int h = 2 * a + r;
+      if (h >= H) continue;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int w = 2 * b + c;
+        if (w >= W) continue;
+        *reinterpret_cast<uint4*>(dx + (((long long)(n * H + h) * W + w) * C8 + cv) * 8) = pack8(acc[r][c]);
+      }
+    }
   }
 }
 
@@ -339,7 +372,7 @@ extern "C" int b2_maxpool_bwd(const void* idx, const void* dy_a, const void* dy_
                               int C, void* stream) {
   if (C % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const int grid = sgrid((long long)N * H * W * (C / 8));
+  const int grid = sgrid((long long)N * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8));
   if (dy_b)
     maxpool_bwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const unsigned char*)idx, (const bf16*)dy_a,
                                                                       (const bf16*)dy_b, (bf16*)dx, N, H, W, C / 8, Ho, Wo);

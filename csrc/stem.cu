@@ -9,7 +9,9 @@
 // A-operand rows straight out of the image (overlapping windows): one box of [<=128 ow x 64 B] per filter row, 7
 // boxes per output row, 64-byte swizzle.  K = 7 * 32 = 224.
 //
-//   fprop : y[(n,oh), ow, 64]  = A[(n,oh,ow), 224] * Wp[64, 224]^T     M = 128 (one output row), N = 64, K-major
+//   fprop : y[(n,oh), ow, 64]  = A[(n,oh,ow), 224] * Wp[64, 224]^T     M = 128 (one output row), N = 64, K-major;
+//           A is not even replicated in shared memory: one TMA box brings the 7 raw padded rows and the operand
+//           descriptor itself (no swizzle, 16-byte row step) expresses the overlapping windows
 //   wgrad : dWp^T[224, 64]     = A[pixels, 224]^T  * dy[pixels, 64]    M = 2 x 128 (k), N = 64, both MN-major,
 //           accumulated in TMEM over all the output rows a CTA owns, one partial per CTA, fixed-order reduce.
 //
@@ -76,29 +78,34 @@ __global__ void stem_wgrad_reduce_kernel(const float* __restrict__ ws, float* __
 // ---------------------------------------------------------------------------------------------- fprop
 // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue, warps 6-9: BatchNorm statistics
 constexpr int kStemFThreads = 320;
-constexpr int kStemAStage = kStemKH * 128 * 64;            // 7 boxes of [128 rows x 64 B]
+// A stage = the 7 raw padded image rows an output row needs (<= 232 pixels x 8 B each), nothing replicated: the
+// A-operand descriptor (K-major, no swizzle) walks them as a Toeplitz matrix - core matrix = 8 output columns x 16 B
+// with rows 16 B apart (the stride-2 window step), next K chunk 16 B further (LBO), next 8 rows 128 B further (SBO).
+constexpr int kStemFStages = 8;
+constexpr int kStemAStage = 13312;                         // >= 6 * 1856 + 16 * 127 + 64 (last window of row 127)
 constexpr int kStemBBytes = kStemKH * kStemCout * 64;      // 7 boxes of [64 rows x 64 B]
 constexpr int kStemPanel = kStemRowsMax * 128;             // output panel: [112 rows x 128 B]
-constexpr int kStemFSmem = kStemStages * kStemAStage + kStemBBytes + 2 * kStemPanel + 1024 + 256;
+constexpr int kStemFSmem = kStemFStages * kStemAStage + kStemBBytes + 2 * kStemPanel + 1024 + 256;
 
 __global__ void __launch_bounds__(kStemFThreads, 1)
     stem_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const __grid_constant__ CUtensorMap tmC, float* __restrict__ stats, int Ho, int num_items) {
+                      const __grid_constant__ CUtensorMap tmC, float* __restrict__ stats, int Ho, int Wo, int pitch,
+                      int num_items) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sB = smem + kStemStages * kStemAStage;
+  uint8_t* sB = smem + kStemFStages * kStemAStage;
   uint8_t* epi = sB + kStemBBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi + 2 * kStemPanel);
   uint64_t* full = bars;                       // [stages]
-  uint64_t* empty = bars + kStemStages;        // [stages]
-  uint64_t* tfull = bars + 2 * kStemStages;    // [2]
+  uint64_t* empty = bars + kStemFStages;        // [stages]
+  uint64_t* tfull = bars + 2 * kStemFStages;    // [2]
   uint64_t* tempty = tfull + 2;                // [2]
   uint64_t* bfull = tempty + 2;                // weights landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStemStages; ++s) {
+    for (int s = 0; s < kStemFStages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
@@ -127,11 +134,10 @@ __global__ void __launch_bounds__(kStemFThreads, 1)
       uint32_t g = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++g) {
         const int n = item / Ho, oh = item - n * Ho;
-        const int s = g % kStemStages;
-        mbar_wait(&empty[s], ((g / kStemStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&full[s], kStemAStage);
-        uint8_t* sA = smem + s * kStemAStage;
-        for (int kh = 0; kh < kStemKH; ++kh) tma_load_4d(sA + kh * 8192, &tmA, &full[s], 0, 0, 2 * oh + kh, n);
+        const int s = g % kStemFStages;
+        mbar_wait(&empty[s], ((g / kStemFStages) & 1) ^ 1);
+        mbar_arrive_expect_tx(&full[s], (uint32_t)(kStemKH * pitch));
+        tma_load_3d(smem + s * kStemAStage, &tmA, &full[s], 0, 2 * oh, n);   // 7 consecutive padded rows
       }
     }
   } else if (warp == 1) {
@@ -142,15 +148,15 @@ __global__ void __launch_bounds__(kStemFThreads, 1)
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++g) {
         const uint32_t acc = g & 1;
         mbar_wait(&tempty[acc], ((g >> 1) & 1) ^ 1);
-        const int s = g % kStemStages;
-        mbar_wait(&full[s], (g / kStemStages) & 1);
+        const int s = g % kStemFStages;
+        mbar_wait(&full[s], (g / kStemFStages) & 1);
         tc_fence_after();
         const uint32_t aBase = smem_u32(smem + s * kStemAStage), bBase = smem_u32(sB);
 #pragma unroll
         for (int kh = 0; kh < kStemKH; ++kh) {
 #pragma unroll
           for (int ks = 0; ks < 2; ++ks) {
-            const uint64_t da = make_smem_desc(aBase + kh * 8192 + ks * 32, 16, 512, 4);
+            const uint64_t da = make_smem_desc(aBase + kh * pitch + ks * 32, 16, 128, 0);
             const uint64_t db = make_smem_desc(bBase + kh * (kStemCout * 64) + ks * 32, 16, 512, 4);
             umma_bf16(tmem_base + acc * kStemCout, da, db, idesc, (kh | ks) != 0);
           }
@@ -235,6 +241,10 @@ __global__ void __launch_bounds__(kStemFThreads, 1)
       if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
       asm volatile("bar.sync 1, 128;" ::: "memory");   // the buffer's previous store has finished reading it
       if (stats) asm volatile("bar.sync %0, 256;" ::"r"(6 + bsel) : "memory");   // ... and the statistics warps
+      if (row >= Wo) {   // rows past the image edge were computed from whatever follows in shared memory
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v0[e] = v1[e] = 0u;
+      }
       if (row < kStemRowsMax) {
         uint8_t* prow = buf + row * 128;
 #pragma unroll
@@ -456,7 +466,12 @@ extern "C" int b2_stem_fprop(const void* xp, const void* wp, void* y, int N, int
   const StemGeom g = stem_geom(H, W);
   CUtensorMap tmA, tmB, tmC;
   int e;
-  if ((e = stem_window_map(&tmA, xp, N, g, 128))) return e;
+  {  // raw padded rows, 8-byte pixels: (pixel | padded row | image), box = 7 whole rows, no swizzle
+    const uint64_t dims[3] = {(uint64_t)g.Wp, (uint64_t)g.Hp, (uint64_t)N};
+    const uint64_t strides[2] = {(uint64_t)g.Wp * 8, (uint64_t)g.Hp * g.Wp * 8};
+    const uint32_t box[3] = {(uint32_t)g.Wp, (uint32_t)kStemKH, 1};
+    if ((e = make_tmap_tiled_u64(&tmA, xp, 3, dims, strides, box))) return e;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)kStemK, (uint64_t)kStemCout};
     const uint64_t strides[1] = {(uint64_t)kStemK * 2};
@@ -473,8 +488,8 @@ extern "C" int b2_stem_fprop(const void* xp, const void* wp, void* y, int N, int
   const int items = N * g.Ho;
   const int grid = items < stem_num_sms() ? items : stem_num_sms();
   const bool with_stats = stats && stats_blocks;
-  stem_fprop_kernel<<<grid, kStemFThreads, kStemFSmem, (cudaStream_t)stream>>>(tmA, tmB, tmC,
-                                                                             with_stats ? stats : nullptr, g.Ho, items);
+  stem_fprop_kernel<<<grid, kStemFThreads, kStemFSmem, (cudaStream_t)stream>>>(
+      tmA, tmB, tmC, with_stats ? stats : nullptr, g.Ho, g.Wo, g.Wp * 8, items);
   if (with_stats) *stats_blocks = 2 * grid;
   return cudaGetLastError();
 }

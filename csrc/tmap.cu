@@ -40,6 +40,21 @@ int make_tmap_tiled_bf16(CUtensorMap* out, const void* base, int rank, const uin
   return (int)r;
 }
 
+int make_tmap_tiled_u64(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                        const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn enc = resolve_encode();
+  if (!enc) return (int)cudaErrorNotSupported;
+  if (rank < 1 || rank > 5) return (int)cudaErrorInvalidValue;
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT64, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, e,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return (int)r;
+}
+
 int make_tmap_panels_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint32_t box_outer,
                           uint32_t panels) {
   EncodeTiledFn enc = resolve_encode();

@@ -19,6 +19,9 @@ int make_tmap_panels_bf16(CUtensorMap* out, const void* base, uint64_t inner, ui
 // of 16, overlapping windows allowed), swizzle_bytes in {0, 32, 64, 128}, zero fill out of bounds.
 int make_tmap_tiled_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                          const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+// Tiled map over 8-byte elements, no swizzle (raw row copies; inner box <= 256 elements = 2 KB).
+int make_tmap_tiled_u64(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                        const uint64_t* strides_bytes, const uint32_t* box);
 // im2col view of an NHWC bf16 tensor [N][H][W][C] (128B swizzle, zero fill): boxes of `channels` x `pixels`,
 // bounding box corners as in cuTensorMapEncodeIm2col (lower = -pad, upper = pad - (K-1)*dilation), traversal stride.
 int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int N, int H, int W, int C, int lower_w, int lower_h,
