@@ -430,6 +430,7 @@ static int pick_bn(int ncols, int force) {
 
 static int g_force_bn = 0;
 static int g_dbg = 0;
+static int g_mt2 = 1;     // v2 wgrad: 256 x 256 tile per CTA where Cout allows (b2_conv_set_wgrad_mt2)
 static int g_panels = 1;  // v2: fetch MN-major operands as one multi-panel TMA box (b2_conv_set_panels)
 static int g_act_mode = -1;  // -1 auto, else force ACT_GATHER / ACT_IM2COL for k>1 or strided convs
 
@@ -468,10 +469,13 @@ constexpr int kThreads2W = 224;  // wgrad (fp32 stores straight from registers) 
 template <int BN>
 constexpr int kStatWarps2 = (BN == 64) ? 4 : 8;
 
-template <int BN>
+// MT = 128-row accumulators per CTA. MT = 2 (wgrad only, BN = 256): one 256 x 256 tile in all 512 TMEM columns - no
+// accumulator double buffering (a wgrad item is one long K loop, there is nothing to overlap), and a third less
+// operand traffic per FLOP, which is what bounds wgrad (its operands come out of L2, not out of a shared weight tile).
+template <int BN, int MT = 1>
 struct Cfg2 {
-  static constexpr int kStageBytes = BM * 128 + BN * 128;
-  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kStageBytes = MT * BM * 128 + BN * 128;
+  static constexpr int kStages = (MT == 2) ? 3 : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
   static constexpr int kEpiBytes = 2 * BM * 128;  // two 128-row x 64-column bf16 panels for the TMA-store epilogue
   static constexpr int kSmem = kStages * kStageBytes + kEpiBytes + 1024 + 256;
 };
@@ -479,13 +483,13 @@ struct Cfg2 {
 struct Item {
   int n0, m0, tap, split, kb_begin, nkb;
 };
-B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn) {
+B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn, int bm = BM) {
   Item it;
   const int nt = item % p.n_tiles;
   int r = item / p.n_tiles;
   const int mt = r % p.m_tiles;
   it.n0 = nt * bn;
-  it.m0 = mt * BM;
+  it.m0 = mt * bm;
   it.tap = 0; it.split = 0; it.kb_begin = 0; it.nkb = p.Kblocks;
   if (kind == WGRAD) {
     const int z = r / p.m_tiles;
@@ -497,11 +501,12 @@ B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn) {
   return it;
 }
 
-template <int KIND, int AMODE, int BN>
+template <int KIND, int AMODE, int BN, int MT = 1>
 __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2), 1)
     igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
-  using C = Cfg2<BN>;
+  using C = Cfg2<BN, MT>;
+  static_assert(MT == 1 || (KIND == WGRAD && BN == 256), "two accumulators per CTA: wgrad, 256-wide tiles only");
   constexpr bool IM2COL = (AMODE == ACT_IM2COL);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -515,7 +520,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  constexpr uint32_t kABytes = BM * 128, kBBytes = BN * 128;
+  constexpr uint32_t kABytes = MT * BM * 128, kBBytes = BN * 128;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::kStages; ++s) {
@@ -545,7 +550,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
     if (lane == 0) {
       uint32_t g = 0;  // global k-block counter (smem ring position carries over from item to item)
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-        const Item it = decode_item(p, item, KIND, BN);
+        const Item it = decode_item(p, item, KIND, BN, MT * BM);
         int iw0 = 0, ih0 = 0, in0 = 0;
         if (IM2COL && KIND != WGRAD) {
           int n, h, w;
@@ -619,7 +624,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
               tma_load_3d(sA, &tmA, &full[s], 0, kb * BK, it.m0 >> 6);
             } else {
 #pragma unroll
-              for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
+              for (int j = 0; j < 2 * MT; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[s], it.m0 + 64 * j, kb * BK);
             }
           } else {
             if (IM2COL) {
@@ -657,9 +662,9 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, kAmn, kBmn);
       uint32_t g = 0, t = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
-        const Item it = decode_item(p, item, KIND, BN);
-        const uint32_t acc = t & 1;
-        mbar_wait(&tempty[acc], ((t >> 1) & 1) ^ 1);  // epilogue has drained this accumulator stage
+        const Item it = decode_item(p, item, KIND, BN, MT * BM);
+        const uint32_t acc = (MT == 2) ? 0u : (t & 1);
+        mbar_wait(&tempty[acc], (((MT == 2) ? t : (t >> 1)) & 1) ^ 1);  // epilogue has drained the accumulator(s)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int i = 0; i < it.nkb; ++i, ++g) {
@@ -676,6 +681,10 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
             const uint64_t db = kBmn ? make_smem_desc_sw128(bBase + k * 2048, 8192, 1024)
                                      : make_smem_desc_sw128(bBase + k * 32, 16, 1024);
             if (!(p.dbg & 2)) umma_bf16(d_tmem, da, db, idesc, (i | k) != 0);
+            if (MT == 2) {   // second 128 rows of the 256-row tile: panels 2,3 of the A stage, columns BN.. of TMEM
+              const uint64_t da2 = make_smem_desc_sw128(aBase + 16384 + k * 2048, 8192, 1024);
+              if (!(p.dbg & 2)) umma_bf16(d_tmem + BN, da2, db, idesc, (i | k) != 0);
+            }
           }
           umma_commit(&empty[s]);
         }
@@ -744,7 +753,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
       };
       uint32_t t = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
-        const Item it = decode_item(p, item, KIND, BN);
+        const Item it = decode_item(p, item, KIND, BN, MT * BM);
         if (it.n0 != st_n0) {
           flush();
           st_n0 = it.n0;
@@ -788,9 +797,9 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
     constexpr int CNT = kEpiThreads2 + 64 * (kStatWarps2<BN> / (2 * P));
     uint32_t t = 0, panel_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
-      const Item it = decode_item(p, item, KIND, BN);
-      const uint32_t acc = t & 1;
-      mbar_wait(&tfull[acc], (t >> 1) & 1);
+      const Item it = decode_item(p, item, KIND, BN, MT * BM);
+      const uint32_t acc = (MT == 2) ? 0u : (t & 1);
+      mbar_wait(&tfull[acc], ((MT == 2) ? t : (t >> 1)) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
       const int m = it.m0 + row;
@@ -899,17 +908,21 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
         }
       } else {
         float* out = reinterpret_cast<float*>(p.out) + (size_t)it.split * p.split_stride;
-        float* orow = out + (size_t)m * p.out_ld + (size_t)it.tap * p.tapC + it.n0;
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          if (ok) {
+        for (int mt = 0; mt < MT; ++mt) {
+          const int mm = m + mt * BM;
+          float* orow = out + (size_t)mm * p.out_ld + (size_t)it.tap * p.tapC + it.n0;
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld32(taddr + mt * BN + c * 32, v);
+            tmem_ld_wait();
+            if (mm < p.M) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-              if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols)
-                st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+              for (int q = 0; q < 8; ++q)
+                if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols)
+                  st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+            }
           }
         }
       }
@@ -1216,7 +1229,7 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int KIND, int AMODE, int BN>
+template <int KIND, int AMODE, int BN, int MT = 1>
 static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p_in, int items,
                            cudaStream_t st) {
   ConvParams p = p_in;
@@ -1226,16 +1239,16 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     int e = make_tmap_2d_bf16(&tmC, p.out, (uint64_t)p.Ncols, (uint64_t)p.M, 64, 128);
     if (e) return (cudaError_t)e;
   }
-  auto kern = igemm2_kernel<KIND, AMODE, BN>;
+  auto kern = igemm2_kernel<KIND, AMODE, BN, MT>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::kSmem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, MT>::kSmem);
     if (e != cudaSuccess) return e;
     configured = true;
   }
   const int grid = items < num_sms() ? items : num_sms();
   const int threads = (KIND == FPROP && p.stats) ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2);
-  kern<<<grid, threads, Cfg2<BN>::kSmem, st>>>(tmA, tmB, tmC, p, items);
+  kern<<<grid, threads, Cfg2<BN, MT>::kSmem, st>>>(tmA, tmB, tmC, p, items);
   return cudaGetLastError();
 }
 template <int KIND, int AMODE>
@@ -1301,6 +1314,7 @@ extern "C" void b2_conv_set_tile_n(int bn) { g_force_bn = bn; }
 extern "C" void b2_conv_set_act_mode(int mode) { g_act_mode = mode; }
 extern "C" void b2_conv_set_debug(int bits) { g_dbg = bits; }
 extern "C" void b2_conv_set_panels(int on) { g_panels = on; }
+extern "C" void b2_conv_set_wgrad_mt2(int on) { g_mt2 = on; }
 
 extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
 
@@ -1499,6 +1513,10 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
   return launch_mode<DGRAD>(mode, bn, tmA, tmB, p, grid, st);
 }
 
+static bool wgrad_mt2(int bn, int Cout) {
+  return g_mt2 && g_impl == 2 && g_act_mode != ACT_GATHER && bn == 256 && Cout % 256 == 0;
+}
+
 // Split-K plan for wgrad: enough work items for ~2-4 per SM, bounded by the workspace.
 extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes) {
   const long long kpix = (long long)N * Ho * Wo;
@@ -1508,6 +1526,10 @@ extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, in
   const long long tiles = flat ? (long long)((Cout + BM - 1) / BM) * ((taps * Cin + 255) / 256)
                                : (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
   long long want = ((g_impl >= 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
+  if (wgrad_mt2(bn, Cout)) {   // half as many (256-row) tiles, one item per SM in a single wave
+    const long long t2 = tiles / 2;
+    want = 148 / t2;
+  }
   const long long wbytes = (long long)Cout * taps * Cin * 4;
   long long cap = ws_bytes / wbytes;
   if (want > cap) want = cap;
@@ -1537,8 +1559,9 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   const bool v2 = g_impl == 2 && mode != ACT_GATHER;   // the persistent (non-pair) kernel runs
   const bool panelsA = g_panels && v2 && Cout % 64 == 0;
   const bool panelsB = g_panels && v2 && mode != ACT_IM2COL;
+  const bool mt2 = v2 && wgrad_mt2(bn, Cout);
   if (panelsA) {
-    if ((e = make_tmap_panels_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, BM / 64))) return e;
+    if ((e = make_tmap_panels_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, (mt2 ? 2 : 1) * BM / 64))) return e;
   } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)kpix, 64, 64))) {
     return e;
   }
@@ -1572,9 +1595,21 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
     p.flatN = 1;
     p.Ncols = taps * Cin;
     p.n_tiles = (p.Ncols + 255) / 256;
-    ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
+    if (mt2) {
+      p.m_tiles = Cout / 256;
+      ce = launch2<WGRAD, ACT_IM2COL, 256, 2>(tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
+    } else {
+      ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * splits, st);
+    }
   } else if (g_impl >= 2 && mode != ACT_GATHER) {
-    ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * taps * splits, st);
+    if (mt2) {
+      p.m_tiles = Cout / 256;
+      const int items = p.n_tiles * p.m_tiles * taps * splits;
+      ce = mode == ACT_TILED ? launch2<WGRAD, ACT_TILED, 256, 2>(tmA, tmB, p, items, st)
+                             : launch2<WGRAD, ACT_IM2COL, 256, 2>(tmA, tmB, p, items, st);
+    } else {
+      ce = launch2_mode<WGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles * taps * splits, st);
+    }
   } else {
     dim3 grid(p.n_tiles, p.m_tiles, taps * splits);
     ce = launch_mode<WGRAD>(mode, bn, tmA, tmB, p, grid, st);

@@ -50,6 +50,8 @@ void b2_conv_set_fuse_stats(int on);
 void b2_conv_set_debug(int bits);
 /* 1 (default): MN-major operands (dgrad weights, wgrad dy / 1x1 x) are fetched as one multi-panel TMA box */
 void b2_conv_set_panels(int on);
+/* 1 (default): wgrad with Cout % 256 == 0 computes one 256 x 256 tile per CTA (all 512 TMEM columns) */
+void b2_conv_set_wgrad_mt2(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* dgrad with the gradient fan-in and the ReLU backward fused into the epilogue: dx = mask ? (dgrad + add) : 0
