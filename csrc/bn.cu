@@ -468,14 +468,39 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
     }                                                                           \
   } while (0)
 
+static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
+                       void* dy, void* dres, long long M, int C, const float* gamma, const float* mean,
+                       const float* invstd, float* dgamma, float* dbeta, int accumulate, int relu, float* coef,
+                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
+
 extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
                          void* dy, void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd,
                          float* dgamma, float* dbeta, int accumulate, int relu, float* coef /*3C*/, float* partial,
                          const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  return bn_bwd_impl(dz_a, dz_b, z, relu_mask, y, dy, dres, M, C, gamma, mean, invstd, dgamma, dbeta, accumulate, relu,
+                     coef, partial, 0, xg, xg_slot, stream);
+}
+
+// Same, but `partial` already holds partial_blocks rows of [2][C] (sum g, sum g*(y-mean)) - produced by the dgrad
+// that computed dz (b2_conv_dgrad_bnstats) - so the reduce pass over dz / y is skipped. Single incoming gradient,
+// no residual-branch output.
+extern "C" int b2_bn_bwd_partial(const void* dz, const void* z, const void* relu_mask, const void* y, void* dy,
+                                 long long M, int C, const float* gamma, const float* mean, const float* invstd,
+                                 float* dgamma, float* dbeta, int accumulate, int relu, float* coef, float* partial,
+                                 int partial_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  if (partial_blocks <= 0 || partial_blocks > kMaxPartialBlocks) return cudaErrorInvalidValue;
+  return bn_bwd_impl(dz, nullptr, z, relu_mask, y, dy, nullptr, M, C, gamma, mean, invstd, dgamma, dbeta, accumulate,
+                     relu, coef, partial, partial_blocks, xg, xg_slot, stream);
+}
+
+static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
+                       void* dy, void* dres, long long M, int C, const float* gamma, const float* mean,
+                       const float* invstd, float* dgamma, float* dbeta, int accumulate, int relu, float* coef,
+                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
   if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
   cudaStream_t st = (cudaStream_t)stream;
   long long rpb;
-  const int nblk = plan_blocks(M, C, &rpb);
+  int nblk = plan_blocks(M, C, &rpb);
   const int RP = kBnThreads / (C / 8);
   const size_t sm = 2 * RP * C * sizeof(float);
   const __nv_bfloat16 *a = (const __nv_bfloat16*)dz_a, *b = (const __nv_bfloat16*)dz_b,
@@ -488,7 +513,10 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
     if (dres) bn_bwd_reduce_kernel<R, T, true><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb); \
     else bn_bwd_reduce_kernel<R, T, false><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb);     \
   } while (0)
-  B2_BWD_DISPATCH(RED, 0);
+  if (given_blocks > 0)
+    nblk = given_blocks;
+  else
+    B2_BWD_DISPATCH(RED, 0);
 #undef RED
   XgpuCtx ctx = xgpu_from_c(xg);
   bn_bwd_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(partial, nblk, C, (float)M, gamma, mean, invstd, dgamma,

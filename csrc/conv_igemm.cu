@@ -51,6 +51,12 @@ struct ConvParams {
   float* stats;
   // dgrad epilogue fusion (v2, TMA-store path): dx = relu_mask ? (acc + add) : 0 — the gradient fan-in of a residual
   // fork and the ReLU backward of the tensor being differentiated, applied before the single bf16 rounding.
+  // dgrad + BatchNorm-backward statistics (v2, TMA-store path): the statistics warps also accumulate, per channel of
+  // dx, sum(g) and sum(g * (y - mean)) with g = relu_mask ? dx : 0 into `stats` - the reduce pass of the BatchNorm
+  // whose output gradient this dgrad produces.
+  const __nv_bfloat16* bwd_y;       // [M][Ncols] pre-BN activations of that BatchNorm
+  const unsigned char* bwd_mask;    // [M][Ncols/8] ReLU mask (nullable: no ReLU)
+  const float* bwd_mean;            // [Ncols]
   const __nv_bfloat16* add;     // [M][Ncols] bf16, optional
   const unsigned char* amask;   // [M][Ncols/8] bits, optional (only with add)
   int panels;  // v2, MN-major operands fetched as one multi-panel TMA box: bit 0 = A (wgrad), bit 1 = B (dgrad/wgrad)
@@ -502,7 +508,7 @@ B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn, int 
 }
 
 template <int KIND, int AMODE, int BN, int MT = 1>
-__global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2), 1)
+__global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<BN> : kThreads2W, 1)
     igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
   using C = Cfg2<BN, MT>;
@@ -700,7 +706,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
     // are zero: their A rows were zero-filled). The sums stay in registers until the CTA moves to another n-tile;
     // a transposing butterfly over the 8 lanes then leaves lane g with channel chunk*8+g, which goes to
     // stats[R*cta + row group][2][Ncols].
-    if (KIND == FPROP && p.stats) {
+    if ((KIND == FPROP || KIND == DGRAD) && p.stats) {
       constexpr int P = BN / 64, NSW = kStatWarps2<BN>, R = NSW / (2 * P), NLD = (BM / R) / 8;
       constexpr int CNT = kEpiThreads2 + 64 * R;
       const int sw = warp - 11, g = lane & 7;
@@ -720,9 +726,9 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
         asm volatile("bar.arrive %0, %1;" ::"r"(6 + pn), "n"(CNT) : "memory");
       }
       const bool rmw = (gridDim.x % p.n_tiles) != 0;   // this CTA comes back to an n-tile it has already flushed
-      float a[8], b[8];
+      float a[8], b[8], mu[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) a[e] = b[e] = 0.f;
+      for (int e = 0; e < 8; ++e) a[e] = b[e] = mu[e] = 0.f;
       int st_n0 = -1;
       auto flush = [&]() {
         if (st_n0 < 0) return;
@@ -757,12 +763,58 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
         if (it.n0 != st_n0) {
           flush();
           st_n0 = it.n0;
+          if (KIND == DGRAD) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mu[e] = __ldg(p.bwd_mean + it.n0 + pn * 64 + chunk * 8 + e);
+          }
         }
         const uint32_t bsel = (P == 1) ? (t & 1) : (pn & 1);
         const uint32_t slot = (P == 1) ? bsel : pn;
-        asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(CNT) : "memory");   // panel written
         const uint32_t src =
             smem_u32(epi_smem) + bsel * (BM * 128) + (rg * (BM / R) + g) * 128 + ((chunk ^ g) << 4);
+        if (KIND == DGRAD) {
+          // BatchNorm-backward sums: 8 rows at a time; the companion loads of the first 8 rows are issued before
+          // waiting for the panel, the panel buffer is handed back after its last shared-memory read.
+          const int col = it.n0 + pn * 64 + chunk * 8;
+          const int row0 = it.m0 + rg * (BM / R) + g;
+#pragma unroll
+          for (int c8 = 0; c8 < NLD / 8; ++c8) {
+            uint4 yv[8];
+            uint32_t mk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = row0 + 8 * (c8 * 8 + i);
+              const bool ok = r < p.M;
+              yv[i] = ok ? ld_nc_v4(p.bwd_y + (size_t)r * p.Ncols + col) : make_uint4(0u, 0u, 0u, 0u);
+              mk[i] = !ok ? 0u : (p.bwd_mask ? (uint32_t)__ldg(p.bwd_mask + (size_t)r * (p.Ncols >> 3) + (col >> 3))
+                                             : 0xffu);
+            }
+            if (c8 == 0) asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(CNT) : "memory");   // panel written
+            uint4 w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[i] = ld_shared_v4(src + (c8 * 8 + i) * 1024);
+            if (c8 == NLD / 8 - 1) {
+              __threadfence_block();
+              asm volatile("bar.arrive %0, %1;" ::"r"(6 + slot), "n"(CNT) : "memory");   // panel buffer free again
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
+              const uint32_t yy[4] = {yv[i].x, yv[i].y, yv[i].z, yv[i].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float glo = ((mk[i] >> (2 * e)) & 1u) ? __uint_as_float(ww[e] << 16) : 0.f;
+                const float ghi = ((mk[i] >> (2 * e + 1)) & 1u) ? __uint_as_float(ww[e] & 0xffff0000u) : 0.f;
+                a[2 * e] += glo;
+                b[2 * e] = fmaf(glo, __uint_as_float(yy[e] << 16) - mu[2 * e], b[2 * e]);
+                a[2 * e + 1] += ghi;
+                b[2 * e + 1] = fmaf(ghi, __uint_as_float(yy[e] & 0xffff0000u) - mu[2 * e + 1], b[2 * e + 1]);
+              }
+            }
+          }
+          continue;
+        }
+        asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(CNT) : "memory");   // panel written
         uint4 w[NLD];
 #pragma unroll
         for (int i = 0; i < NLD; ++i) w[i] = ld_shared_v4(src + i * 1024);
@@ -792,7 +844,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
     const int row = quad * 32 + lane;
     const bool store_thread = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
     const bool tma_epi = (KIND != WGRAD) && p.cls == 1;
-    const bool with_stats = (KIND == FPROP) && p.stats != nullptr;
+    const bool with_stats = (KIND != WGRAD) && p.stats != nullptr;
     constexpr int P = BN / 64;
     constexpr int CNT = kEpiThreads2 + 64 * (kStatWarps2<BN> / (2 * P));
     uint32_t t = 0, panel_seq = 0;
@@ -857,7 +909,7 @@ __global__ void __launch_bounds__(KIND == FPROP ? kThreads2 + 32 * kStatWarps2<B
           // the panel buffer is needed only now: its previous TMA store has finished reading it ...
           if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
-          if (with_stats)   // ... and so have the statistics warps
+          if (KIND != WGRAD && with_stats)   // ... and so have the statistics warps
             asm volatile("bar.sync %0, %1;" ::"r"(6 + (P == 1 ? bsel : (pn + P - 2) % P)), "n"(CNT) : "memory");
           uint8_t* prow = buf + row * 128;
 #pragma unroll
@@ -1247,7 +1299,7 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     configured = true;
   }
   const int grid = items < num_sms() ? items : num_sms();
-  const int threads = (KIND == FPROP && p.stats) ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2);
+  const int threads = (KIND != WGRAD && p.stats) ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2);
   kern<<<grid, threads, Cfg2<BN, MT>::kSmem, st>>>(tmA, tmB, tmC, p, items);
   return cudaGetLastError();
 }
@@ -1446,8 +1498,16 @@ static int dgrad_strided_v2(const void* dy, const void* w, void* dx, int N, int 
   return 0;
 }
 
+struct DgradBn {   // optional BatchNorm-backward statistics request (see ConvParams::bwd_y)
+  const void* y;
+  const void* mask;
+  const float* mean;
+  float* partial;
+  int* blocks;
+};
 static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
-                           int KW, int stride, int pad, const void* add, const void* mask, void* stream);
+                           int KW, int stride, int pad, const void* add, const void* mask, void* stream,
+                           const DgradBn* bn = nullptr);
 
 extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
                              int KW, int stride, int pad, void* stream) {
@@ -1466,8 +1526,21 @@ extern "C" int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int 
   return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, add, mask, stream);
 }
 
+// dgrad that also leaves the partial sums of the BatchNorm backward of dx behind (dx is the gradient of that
+// BatchNorm's ReLU output): partial receives [*blocks][2][Cin] rows of (sum g, sum g*(y-mean)), g = mask ? dx : 0,
+// to be handed to b2_bn_bwd_partial. *blocks == 0: not produced by the active kernel variant (run the reduce pass).
+extern "C" int b2_conv_dgrad_bnstats(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                     int KH, int KW, int stride, int pad, const void* bn_y, const void* bn_mask,
+                                     const float* bn_mean, float* partial, int* blocks, void* stream) {
+  if (!blocks || !partial || !bn_y || !bn_mean) return cudaErrorInvalidValue;
+  *blocks = 0;
+  DgradBn bn{bn_y, bn_mask, bn_mean, partial, blocks};
+  return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, nullptr, nullptr, stream, &bn);
+}
+
 static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
-                           int KW, int stride, int pad, const void* add, const void* mask, void* stream) {
+                           int KW, int stride, int pad, const void* add, const void* mask, void* stream,
+                           const DgradBn* bnreq) {
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * H * W;
@@ -1508,7 +1581,18 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
     p.m_tiles = (M + 2 * BM - 1) / (2 * BM);
     return launch3_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
   }
-  if (g_impl >= 2 && mode != ACT_GATHER) return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
+  if (g_impl >= 2 && mode != ACT_GATHER) {
+    const int items = p.n_tiles * p.m_tiles;
+    if (bnreq && g_fuse_stats && g_impl == 2 && Cin % bn == 0) {   // TMA-store epilogue, every panel exists
+      const int grid = items < num_sms() ? items : num_sms();       // must match launch2()
+      p.stats = bnreq->partial;
+      p.bwd_y = (const __nv_bfloat16*)bnreq->y;
+      p.bwd_mask = (const unsigned char*)bnreq->mask;
+      p.bwd_mean = bnreq->mean;
+      *bnreq->blocks = (bn == 256 ? 1 : 2) * grid;
+    }
+    return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, items, st);
+  }
   dim3 grid(p.n_tiles, p.m_tiles, 1);
   return launch_mode<DGRAD>(mode, bn, tmA, tmB, p, grid, st);
 }

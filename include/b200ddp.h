@@ -54,6 +54,13 @@ void b2_conv_set_panels(int on);
 void b2_conv_set_wgrad_mt2(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
+/* dgrad that also produces the partial sums of the BatchNorm backward whose output gradient it computes (statistics
+ * warps of the persistent kernel): partial receives [*blocks][2][Cin] rows of (sum g, sum g*(y-mean)) with
+ * g = mask ? dx : 0; hand them to b2_bn_bwd_partial. *blocks == 0: not produced, run b2_bn_bwd as usual.
+ * partial must hold 2 * (number of SMs) * 2 * Cin floats. */
+int b2_conv_dgrad_bnstats(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                          int KW, int stride, int pad, const void* bn_y, const void* bn_mask, const float* bn_mean,
+                          float* partial, int* blocks, void* stream);
 /* dgrad with the gradient fan-in and the ReLU backward fused into the epilogue: dx = mask ? (dgrad + add) : 0
  * (add: bf16 NHWC like dx; mask: 1 bit per element as written by b2_bn_fwd_train, nullable). Returns -1 without
  * launching anything when the active kernel variant cannot fuse it. */
@@ -117,6 +124,12 @@ int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* rel
               void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
               int accumulate, int relu, float* coef, float* partial, const b2_xgpu_ctx* xg, int xg_slot,
               void* stream);
+/* Same for a single incoming gradient whose reduce pass already happened: partial holds partial_blocks rows of
+ * [2][C] written by b2_conv_dgrad_bnstats. */
+int b2_bn_bwd_partial(const void* dz, const void* z, const void* relu_mask, const void* y, void* dy, long long M,
+                      int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
+                      int accumulate, int relu, float* coef, float* partial, int partial_blocks,
+                      const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Pooling, loss, optimizer, stem helpers (csrc/misc.cu).

@@ -219,6 +219,9 @@ class ResNetEngine:
         # epilogue's row-per-thread reads of the skip gradient cost more than the BatchNorm-backward bytes they save
         # (measured: R50 bs256 dgrad +3.0 ms vs BN reduce -1.2 ms).
         self.fuse_fanin = os.environ.get("B200DDP_FUSE_FANIN", "0") == "1"
+        # the dgrad that produces a BatchNorm's output gradient also produces that BatchNorm's backward sums
+        self.fuse_bn_bwd = os.environ.get("B200DDP_FUSE_BN_BWD", "1") != "0"
+        self._bn_blocks = 0
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
         self.xg_slot = 0           # float offset of the statistics exchange area inside the symmetric window
@@ -364,17 +367,27 @@ class ResNetEngine:
         writer(out, False)
         return out
 
-    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, dx_add=None, dx_mask=None):
+    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, dx_add=None, dx_mask=None,
+                  given_blocks=0, next_rec=None):
         """Backward of one conv+BN(+ReLU) unit. ``pre_masked``: dz_a already is the complete, ReLU-masked gradient
         of this unit's output (produced by a fused dgrad epilogue), so it doubles as the residual-branch gradient.
         ``dx_add`` / ``dx_mask``: fan-in gradient (and the ReLU mask of this unit's input) to fuse into the dgrad
-        epilogue; the returned flag says whether that happened."""
+        epilogue; the returned flag says whether that happened. ``given_blocks`` > 0: the dgrad that produced dz_a
+        already left this BatchNorm's backward sums in ``native.bn_partial_b`` (the reduce pass is skipped).
+        ``next_rec``: the unit whose BatchNorm consumes this unit's dx - its backward sums are produced by this
+        unit's dgrad and the block count is left in ``self._bn_blocks``."""
         conv, bn = rec.conv, rec.bn
         st = self._bn(bn)
         # BN backward needs dgamma/dbeta destinations up front (the finalize kernel writes them).
         dg_slot = self._slot(bn.weight)
         db_slot = self._slot(bn.bias)
-        if pre_masked:
+        if given_blocks > 0:
+            dy = native.bn_bwd_partial(dz_a, rec.y, bn.weight, st.mean, st.invstd, dg_slot[0], db_slot[0],
+                                       dg_slot[1] and db_slot[1], rec.relu, st.coef,
+                                       native.bn_partial_b(self.device), given_blocks,
+                                       self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
+            dres = None
+        elif pre_masked:
             dy, _ = native.bn_bwd(dz_a, None, None, rec.y, bn.weight, st.mean, st.invstd,
                                   dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], False, st.coef, False,
                                   self._sync_bn_ctx(bn), self.xg_slot, None)
@@ -404,6 +417,12 @@ class ResNetEngine:
         if need_dx and dx_add is not None:
             dx = convops.conv_dgrad_fused(dy, self._w16(w), rec.x.shape, s, pd, dx_add, dx_mask)
             fused = dx is not None
+        self._bn_blocks = 0
+        if need_dx and dx is None and next_rec is not None and self.fuse_bn_bwd and next_rec.relu:
+            nst = self._bn(next_rec.bn)
+            dx, self._bn_blocks = convops.conv_dgrad_bnstats(dy, self._w16(w), rec.x.shape, s, pd, next_rec.y,
+                                                             next_rec.mask, nst.mean,
+                                                             native.bn_partial_b(self.device))
         if need_dx and dx is None:
             dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd)
         g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
@@ -446,9 +465,15 @@ class ResNetEngine:
             recs_main = bt[:n_main - 1]
             rec_ds = bt[n_main - 1] if blk.downsample is not None else None
             rec_last = bt[-1]
-            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_masked)
-            for rec in reversed(recs_main[1:]):
-                d, _ = self._unit_bwd(rec, d, None, True, False, grads)
+            # each dgrad of the main path also produces the BatchNorm-backward sums of the unit it feeds
+            chain = list(recs_main)            # first .. last-but-one unit of the main path
+            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_masked,
+                                     next_rec=chain[-1])
+            blocks_first = self._bn_blocks
+            for j in range(len(chain) - 1, 0, -1):
+                d, _ = self._unit_bwd(chain[j], d, None, True, False, grads, given_blocks=self._bn_blocks,
+                                      next_rec=chain[j - 1])
+                blocks_first = self._bn_blocks
             # gradient of the block input = dgrad(first conv) + skip-path gradient, masked by the ReLU that produced
             # the input (the previous block's output ReLU): both fused into the first conv's dgrad epilogue
             skip = dres
@@ -456,9 +481,11 @@ class ResNetEngine:
                 skip, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
             prev_mask = rev[i + 1][1][-1].mask if i + 1 < len(rev) else None
             if self.fuse_fanin:
-                d, fused = self._unit_bwd(recs_main[0], d, None, True, False, grads, dx_add=skip, dx_mask=prev_mask)
+                d, fused = self._unit_bwd(recs_main[0], d, None, True, False, grads, dx_add=skip, dx_mask=prev_mask,
+                                          given_blocks=blocks_first)
             else:
-                (d, _), fused = self._unit_bwd(recs_main[0], d, None, True, False, grads), False
+                (d, _), fused = self._unit_bwd(recs_main[0], d, None, True, False, grads,
+                                               given_blocks=blocks_first), False
             if fused:
                 da, db, pre_masked = d, None, prev_mask is not None
             else:

@@ -132,6 +132,22 @@ def conv_dgrad_fused(dy, w, x_shape, stride, pad, add, mask=None):
     return dx
 
 
+def conv_dgrad_bnstats(dy, w, x_shape, stride, pad, bn_y, bn_mask, bn_mean, partial):
+    """conv_dgrad whose statistics warps also produce the reduce pass of the BatchNorm backward that consumes dx
+    (dx = gradient of relu(bn(bn_y))). Returns (dx, blocks); blocks == 0: not produced, run the normal bn_bwd."""
+    N, Cin, H, W = x_shape
+    Cout, _, KH, KW = w.shape
+    assert _is_cl(dy) and _is_cl(w) and _is_cl(bn_y) and tuple(bn_y.shape) == tuple(x_shape)
+    dx = torch.empty((N, Cin, H, W), dtype=torch.bfloat16, device=dy.device, memory_format=torch.channels_last)
+    blocks = ctypes.c_int(0)
+    e = _lib.lib().b2_conv_dgrad_bnstats(_lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), N, H, W, Cin, Cout, KH, KW, stride,
+                                         pad, _lib.ptr(bn_y), _lib.ptr(bn_mask), _lib.ptr(bn_mean), _lib.ptr(partial),
+                                         ctypes.byref(blocks), _lib.stream_ptr())
+    _lib.check(e, "b2_conv_dgrad_bnstats")
+    _lib.count_launch()
+    return dx, blocks.value
+
+
 def conv_dgrad(dy, w, x_shape, stride, pad):
     N, Cin, H, W = x_shape
     Cout, _, KH, KW = w.shape

@@ -79,6 +79,25 @@ def bn_fwd_eval(y, res, gamma, beta, running_mean, running_var, eps, relu, scale
     return z
 
 
+def bn_partial_b(device):
+    """Second partial-sum scratch: holds the BatchNorm-backward sums a dgrad produced for the NEXT unit while other
+    BatchNorm kernels (e.g. the downsample branch) use bn_partial in between."""
+    return scratch(device, "bn_partial_b", 592 * 2 * 2048)
+
+
+def bn_bwd_partial(dz, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, partial, partial_blocks,
+                   xg=None, xg_slot=0, mask=None):
+    """bn_bwd for a single incoming gradient whose reduce pass was done by the dgrad that produced it."""
+    M, C = _mc(y)
+    dy = torch.empty_like(y)
+    e = _lib.lib().b2_bn_bwd_partial(ptr(dz), None, ptr(mask), ptr(y), ptr(dy), c_ll(M), C, ptr(gamma), ptr(mean),
+                                     ptr(invstd), ptr(dgamma), ptr(dbeta), int(accumulate), int(relu), ptr(coef),
+                                     ptr(partial), int(partial_blocks), _xg(xg), xg_slot, stream_ptr())
+    check(e, "b2_bn_bwd_partial")
+    count_launch(2)
+    return dy
+
+
 def bn_bwd(dz_a, dz_b, z, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, want_dres, xg=None,
            xg_slot=0, mask=None):
     """aten::native_batch_norm_backward + threshold_backward + the gradient fan-in add, fused.

@@ -282,3 +282,30 @@ def test_conv_dgrad_epilogue_fan_in_and_relu_mask(ci, co, k, p, H, N):
     assert (got.float()[~keep.permute(0, 3, 1, 2)] == 0).all()
     got2 = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, None)
     assert _rel(got2, conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p) + add.float()) < 1e-2
+
+
+@pytest.mark.parametrize("ci,co,k,p,H,N", [(64, 256, 1, 0, 28, 4), (128, 128, 3, 1, 14, 3), (256, 1024, 1, 0, 14, 5),
+                                            (512, 512, 3, 1, 7, 6)])
+def test_conv_dgrad_produces_bn_backward_sums(ci, co, k, p, H, N):
+    """The dgrad kernel's statistics warps leave sum(g), sum(g*(y-mean)) per channel of dx (g = mask ? dx : 0)."""
+    from pytorch_distributed_tutorials_b200.ops import conv, native
+    torch.manual_seed(9)
+    w = _bf(torch.randn(co, ci, k, k, device=DEV) / (ci * k * k) ** 0.5)
+    dy = _bf(torch.randn(N, co, H, H, device=DEV))
+    y = _bf(torch.randn(N, ci, H, H, device=DEV))
+    mean = torch.randn(ci, device=DEV) * 0.1
+    keep = torch.rand(N, H, H, ci, device=DEV) > 0.5
+    bits = (keep.view(N, H, H, ci // 8, 8).to(torch.uint8) << torch.arange(8, device=DEV, dtype=torch.uint8)).sum(
+        -1).to(torch.uint8)
+    partial = native.bn_partial_b(torch.device(DEV))
+    partial.fill_(float("nan"))
+    dx, blocks = conv.conv_dgrad_bnstats(dy, w, (N, ci, H, H), 1, p, y, bits, mean, partial)
+    torch.cuda.synchronize()
+    assert blocks > 0
+    assert _rel(dx, conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p)) < 1e-2
+    part = partial[: blocks * 2 * ci].view(blocks, 2, ci).sum(0)
+    g = torch.where(keep.permute(0, 3, 1, 2), dx.float(), torch.zeros((), device=DEV))
+    ref0 = g.sum((0, 2, 3))
+    ref1 = (g * (y.float() - mean.view(1, -1, 1, 1))).sum((0, 2, 3))
+    assert torch.allclose(part[0], ref0, rtol=1e-3, atol=5e-2), (part[0] - ref0).abs().max()
+    assert torch.allclose(part[1], ref1, rtol=1e-3, atol=5e-2), (part[1] - ref1).abs().max()
