@@ -49,14 +49,16 @@ struct ConvParams {
   // fprop (v2): per-CTA partial BatchNorm statistics of the bf16 output, [gridDim][2][Ncols] fp32 (sum, sum of
   // squares), accumulated tile by tile in a fixed order -> deterministic. nullptr = not requested.
   float* stats;
-  // dgrad epilogue fusion (v2, TMA-store path): dx = relu_mask ? (acc + add) : 0 — the gradient fan-in of a residual
-  // fork and the ReLU backward of the tensor being differentiated, applied before the single bf16 rounding.
+  // dgrad fan-in fusion (v2, TMA-store path): dx = relu_mask ? (dgrad + add) : 0 — the gradient fan-in of a residual
+  // fork and the ReLU backward of the tensor being differentiated, done by the statistics warps on the bf16 panel in
+  // shared memory (coalesced companion loads), together with the BatchNorm-backward sums of that tensor.
   // dgrad + BatchNorm-backward statistics (v2, TMA-store path): the statistics warps also accumulate, per channel of
   // dx, sum(g) and sum(g * (y - mean)) with g = relu_mask ? dx : 0 into `stats` - the reduce pass of the BatchNorm
   // whose output gradient this dgrad produces.
   const __nv_bfloat16* bwd_y;       // [M][Ncols] pre-BN activations of that BatchNorm
   const unsigned char* bwd_mask;    // [M][Ncols/8] ReLU mask (nullable: no ReLU)
   const float* bwd_mean;            // [Ncols]
+  int fanin;                    // 1: the statistics warps add `add`, apply `amask`, write the panel back and store it
   const __nv_bfloat16* add;     // [M][Ncols] bf16, optional
   const unsigned char* amask;   // [M][Ncols/8] bits, optional (only with add)
   int panels;  // v2, MN-major operands fetched as one multi-panel TMA box: bit 0 = A (wgrad), bit 1 = B (dgrad/wgrad)
@@ -507,8 +509,10 @@ B2_DEVICE Item decode_item(const ConvParams& p, int item, int kind, int bn, int 
   return it;
 }
 
-template <int KIND, int AMODE, int BN, int MT = 1>
-__global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<BN> : kThreads2W, 1)
+// FAN = 1 (dgrad only): the fan-in variant - the statistics warps finish the panel (skip add, ReLU mask) and a store
+// warp writes it out; a separate instantiation so that the default kernels do not carry its code and registers.
+template <int KIND, int AMODE, int BN, int MT = 1, int FAN = 0>
+__global__ void __launch_bounds__(KIND == WGRAD ? kThreads2W : kThreads2 + 32 * kStatWarps2<BN> + (FAN ? 32 : 0), 1)
     igemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, const ConvParams p, int num_items) {
   using C = Cfg2<BN, MT>;
@@ -706,7 +710,177 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
     // are zero: their A rows were zero-filled). The sums stay in registers until the CTA moves to another n-tile;
     // a transposing butterfly over the 8 lanes then leaves lane g with channel chunk*8+g, which goes to
     // stats[R*cta + row group][2][Ncols].
-    if ((KIND == FPROP || KIND == DGRAD) && p.stats) {
+    if (KIND == DGRAD && FAN) {
+      // ---- fan-in mode: ALL statistics warps work on every panel (4 or 8 rows per thread). They add the skip-path
+      // gradient, apply the ReLU mask of the tensor being differentiated, write the finished bf16 panel back, one
+      // warp issues the TMA store (and alone hands the buffer back once the store has read it), and the
+      // BatchNorm-backward sums sum(g), sum(g*y) are butterfly-reduced per panel. The companion tensors of the NEXT
+      // panel are loaded into registers before waiting for it, so their latency is hidden behind the pipeline.
+      constexpr int P = BN / 64, NSW = kStatWarps2<BN>, RQ = NSW / 2, NROW = BM / RQ / 8, T = NSW * 32;
+      const int sw = warp - 11, g = lane & 7, q = sw >> 1;
+      const int chunk = (sw & 1) * 4 + (lane >> 3);
+      if (sw == NSW) {
+        // ---- store warp: waits until a panel is final, issues its TMA store and hands the buffer back to the
+        // epilogue as soon as the store has read it; the statistics warps never block on a store
+        asm volatile("bar.arrive %0, %1;" ::"r"(P == 1 ? 6 : 6 + P - 2), "n"(kEpiThreads2 + 32) : "memory");
+        asm volatile("bar.arrive %0, %1;" ::"r"(P == 1 ? 7 : 6 + P - 1), "n"(kEpiThreads2 + 32) : "memory");
+        uint32_t t = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
+          const Item it = decode_item(p, item, KIND, BN, MT * BM);
+#pragma unroll 1
+          for (int pn = 0; pn < P; ++pn) {
+            const uint32_t bsel = (P == 1) ? (t & 1) : (pn & 1);
+            const uint32_t slot = (P == 1) ? bsel : pn;
+            asm volatile("bar.sync %0, %1;" ::"r"(11 + (int)bsel), "n"(T + 32) : "memory");   // the panel is final
+            if (lane == 0) {
+              tma_store_2d(epi_smem + bsel * (BM * 128), &tmC, it.n0 + pn * 64, it.m0);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            }
+            __syncwarp();
+            asm volatile("bar.arrive %0, %1;" ::"r"(6 + slot), "n"(kEpiThreads2 + 32) : "memory");   // buffer free
+          }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have landed
+      } else {
+      const bool sums = p.stats != nullptr && p.bwd_y != nullptr;   // also produce the BatchNorm-backward sums
+      if (sums) {
+        float4* z = reinterpret_cast<float4*>(p.stats + (size_t)blockIdx.x * RQ * 2 * p.Ncols);
+        for (int i = threadIdx.x - kThreads2; i < RQ * 2 * p.Ncols / 4; i += T) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      asm volatile("bar.sync 10, %0;" ::"n"(T) : "memory");
+      const bool rmw = (gridDim.x % p.n_tiles) != 0;
+      uint4 sk[NROW], yv[NROW];
+      uint32_t mk[NROW];
+      auto load_companions = [&](int item_, int pn_) {
+        const Item i2 = decode_item(p, item_, KIND, BN, MT * BM);
+        const int col = i2.n0 + pn_ * 64 + chunk * 8;
+        const int row0 = i2.m0 + q * (BM / RQ) + g;
+#pragma unroll
+        for (int i = 0; i < NROW; ++i) {
+          const int r = row0 + 8 * i;
+          const bool ok = r < p.M;
+          const size_t off = (size_t)r * p.Ncols + col;
+          sk[i] = ok ? ld_nc_v4(p.add + off) : make_uint4(0u, 0u, 0u, 0u);
+          if (sums) yv[i] = ok ? ld_nc_v4(p.bwd_y + off) : make_uint4(0u, 0u, 0u, 0u);
+          mk[i] = !ok ? 0u : (p.amask ? (uint32_t)__ldg(p.amask + (off >> 3)) : 0xffu);
+        }
+      };
+      float st_a[P], st_b[P];
+#pragma unroll
+      for (int j = 0; j < P; ++j) st_a[j] = st_b[j] = 0.f;
+      int st_n0 = -1;
+      auto flush = [&]() {
+        if (st_n0 < 0) return;
+        float* dst = p.stats + (size_t)(blockIdx.x * RQ + q) * 2 * p.Ncols;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+          const int gc = st_n0 + j * 64 + chunk * 8 + g;
+          if (gc < p.Ncols) {
+            const float s0 = st_a[j], s1 = st_b[j] - __ldg(p.bwd_mean + gc) * st_a[j];   // sum g*(y - mean)
+            if (rmw) {
+              dst[gc] += s0;
+              dst[p.Ncols + gc] += s1;
+            } else {
+              dst[gc] = s0;
+              dst[p.Ncols + gc] = s1;
+            }
+          }
+          st_a[j] = st_b[j] = 0.f;
+        }
+      };
+      int item = blockIdx.x;
+      if (item < num_items) load_companions(item, 0);
+      uint32_t t = 0;
+      for (; item < num_items; item += gridDim.x, ++t) {
+        const Item it = decode_item(p, item, KIND, BN, MT * BM);
+        if (sums && it.n0 != st_n0) {
+          flush();
+          st_n0 = it.n0;
+        }
+        if (item + (int)gridDim.x < num_items) {
+          // pull the companion lines of the NEXT tile into L2 now (a whole tile ahead): the register loads issued
+          // one panel ahead then only pay the L2 latency. 8 threads share a row: 4 take the skip-gradient lines, 4
+          // the activation lines (one 128-byte line per 64 columns).
+          const Item nx = decode_item(p, item + (int)gridDim.x, KIND, BN, MT * BM);
+          if ((chunk & 3) < P && (chunk < 4 || sums)) {
+            const __nv_bfloat16* base = (chunk < 4 ? p.add : p.bwd_y) + nx.n0 + (chunk & 3) * 64;
+#pragma unroll
+            for (int i = 0; i < NROW; ++i) {
+              const int r = nx.m0 + q * (BM / RQ) + g + 8 * i;
+              if (r < p.M) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)r * p.Ncols));
+                if (chunk == 0 && p.amask)
+                  asm volatile("prefetch.global.L2 [%0];" ::"l"(p.amask + (((size_t)r * p.Ncols + nx.n0) >> 3)));
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int pn = 0; pn < P; ++pn) {
+          const uint32_t bsel = (P == 1) ? (t & 1) : (pn & 1);
+          const uint32_t slot = (P == 1) ? bsel : pn;
+          asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(kEpiThreads2 + T) : "memory");   // panel written
+          uint8_t* pbase = epi_smem + bsel * (BM * 128) + (q * (BM / RQ) + g) * 128 + ((chunk ^ g) << 4);
+          float a[8], b[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) a[e] = b[e] = 0.f;
+#pragma unroll
+          for (int i = 0; i < NROW; ++i) {
+            uint4* cell = reinterpret_cast<uint4*>(pbase + i * 1024);
+            const uint4 w4 = *cell;
+            const uint32_t ww[4] = {w4.x, w4.y, w4.z, w4.w};
+            const uint32_t ss[4] = {sk[i].x, sk[i].y, sk[i].z, sk[i].w};
+            const uint32_t yy[4] = {yv[i].x, yv[i].y, yv[i].z, yv[i].w};
+            uint32_t oo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              // packed bf16x2 add (one rounding, as fp32 add + round), then the two mask bits pick bytes or zero
+              __nv_bfloat162 wv = *reinterpret_cast<const __nv_bfloat162*>(&ww[e]);
+              __nv_bfloat162 sv = *reinterpret_cast<const __nv_bfloat162*>(&ss[e]);
+              const __nv_bfloat162 sum2 = __hadd2(wv, sv);
+              const uint32_t sel = (uint32_t)(0x3210324444104444ull >> (16 * ((mk[i] >> (2 * e)) & 3u))) & 0xffffu;
+              oo[e] = __byte_perm(*reinterpret_cast<const uint32_t*>(&sum2), 0u, sel);
+              if (sums) {
+                const float glo = __uint_as_float(oo[e] << 16), ghi = __uint_as_float(oo[e] & 0xffff0000u);
+                a[2 * e] += glo;
+                b[2 * e] = fmaf(glo, __uint_as_float(yy[e] << 16), b[2 * e]);
+                a[2 * e + 1] += ghi;
+                b[2 * e + 1] = fmaf(ghi, __uint_as_float(yy[e] & 0xffff0000u), b[2 * e + 1]);
+              }
+            }
+            *cell = make_uint4(oo[0], oo[1], oo[2], oo[3]);
+          }
+          fence_proxy_async_smem();
+          // the companion registers are free: fetch the next panel's while this one is stored
+          if (pn + 1 < P) {
+            load_companions(item, pn + 1);
+          } else if (item + (int)gridDim.x < num_items) {
+            load_companions(item + (int)gridDim.x, 0);
+          }
+          // this thread's part of the panel is final: tell the store warp (one barrier per panel buffer)
+          asm volatile("bar.arrive %0, %1;" ::"r"(11 + (int)bsel), "n"(T + 32) : "memory");
+          (void)slot;
+          if (sums) {
+#pragma unroll
+            for (int w = 4; w >= 1; w >>= 1) {
+              const bool up = (g & w) != 0;
+#pragma unroll
+              for (int j = 0; j < w; ++j) {
+                const float sa = up ? a[j] : a[j + w], ka = up ? a[j + w] : a[j];
+                const float sb = up ? b[j] : b[j + w], kb = up ? b[j + w] : b[j];
+                a[j] = ka + __shfl_xor_sync(0xffffffffu, sa, w);
+                b[j] = kb + __shfl_xor_sync(0xffffffffu, sb, w);
+              }
+            }
+            st_a[pn] += a[0];
+            st_b[pn] += b[0];
+          }
+        }
+      }
+      if (sums) flush();
+      }
+    } else if ((KIND == FPROP || KIND == DGRAD) && p.stats) {
       constexpr int P = BN / 64, NSW = kStatWarps2<BN>, R = NSW / (2 * P), NLD = (BM / R) / 8;
       constexpr int CNT = kEpiThreads2 + 64 * R;
       const int sw = warp - 11, g = lane & 7;
@@ -773,32 +947,33 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
         const uint32_t src =
             smem_u32(epi_smem) + bsel * (BM * 128) + (rg * (BM / R) + g) * 128 + ((chunk ^ g) << 4);
         if (KIND == DGRAD) {
-          // BatchNorm-backward sums: 8 rows at a time; the companion loads of the first 8 rows are issued before
+          // BatchNorm-backward sums: CH rows at a time; the companion loads of the first CH rows are issued before
           // waiting for the panel, the panel buffer is handed back after its last shared-memory read.
+          constexpr int CH = (BN >= 128) ? 4 : 8;   // 4 keeps the wide variants (96-register cap) out of local memory
           const int col = it.n0 + pn * 64 + chunk * 8;
           const int row0 = it.m0 + rg * (BM / R) + g;
 #pragma unroll
-          for (int c8 = 0; c8 < NLD / 8; ++c8) {
-            uint4 yv[8];
-            uint32_t mk[8];
+          for (int c8 = 0; c8 < NLD / CH; ++c8) {
+            uint4 yv[CH];
+            uint32_t mk[CH];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int r = row0 + 8 * (c8 * 8 + i);
+            for (int i = 0; i < CH; ++i) {
+              const int r = row0 + 8 * (c8 * CH + i);
               const bool ok = r < p.M;
               yv[i] = ok ? ld_nc_v4(p.bwd_y + (size_t)r * p.Ncols + col) : make_uint4(0u, 0u, 0u, 0u);
               mk[i] = !ok ? 0u : (p.bwd_mask ? (uint32_t)__ldg(p.bwd_mask + (size_t)r * (p.Ncols >> 3) + (col >> 3))
                                              : 0xffu);
             }
             if (c8 == 0) asm volatile("bar.sync %0, %1;" ::"r"(2 + slot), "n"(CNT) : "memory");   // panel written
-            uint4 w[8];
+            uint4 w[CH];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) w[i] = ld_shared_v4(src + (c8 * 8 + i) * 1024);
-            if (c8 == NLD / 8 - 1) {
+            for (int i = 0; i < CH; ++i) w[i] = ld_shared_v4(src + (c8 * CH + i) * 1024);
+            if (c8 == NLD / CH - 1) {
               __threadfence_block();
               asm volatile("bar.arrive %0, %1;" ::"r"(6 + slot), "n"(CNT) : "memory");   // panel buffer free again
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < CH; ++i) {
               const uint32_t ww[4] = {w[i].x, w[i].y, w[i].z, w[i].w};
               const uint32_t yy[4] = {yv[i].x, yv[i].y, yv[i].z, yv[i].w};
 #pragma unroll
@@ -844,9 +1019,12 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
     const int row = quad * 32 + lane;
     const bool store_thread = (threadIdx.x == 64);  // first epilogue thread issues the TMA stores
     const bool tma_epi = (KIND != WGRAD) && p.cls == 1;
-    const bool with_stats = (KIND != WGRAD) && p.stats != nullptr;
+    const bool with_stats = (KIND != WGRAD) && (p.stats != nullptr || (KIND == DGRAD && FAN != 0));
     constexpr int P = BN / 64;
     constexpr int CNT = kEpiThreads2 + 64 * (kStatWarps2<BN> / (2 * P));
+    constexpr bool fan = (KIND == DGRAD) && FAN != 0;
+    const int free_cnt = fan ? kEpiThreads2 + 32 : CNT;   // fan-in mode: only the storing warp hands a buffer back
+    const int full_cnt = fan ? kEpiThreads2 + 32 * kStatWarps2<BN> : CNT;   // ... and every statistics warp takes it
     uint32_t t = 0, panel_seq = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
       const Item it = decode_item(p, item, KIND, BN, MT * BM);
@@ -865,33 +1043,9 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
           if (it.n0 + pn * 64 >= p.Ncols) break;
           const uint32_t bsel = panel_seq & 1;
           uint8_t* buf = epi_smem + bsel * (BM * 128);
-          uint4 addv[4];
-          uint32_t mbits = 0xffffffffu;
-          const bool fuse_add = (KIND == DGRAD) && p.add != nullptr && ok;
-          if (KIND == DGRAD && fuse_add) {   // issued before the TMEM load so that the two latencies overlap
-            const int col0 = it.n0 + pn * 64 + eg * 32;
-            const __nv_bfloat16* ap = p.add + (size_t)m * p.Ncols + col0;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) addv[q] = ld_nc_v4(ap + 8 * q);
-            if (p.amask)
-              mbits = __ldg(reinterpret_cast<const unsigned int*>(p.amask + (size_t)m * (p.Ncols >> 3) + (col0 >> 3)));
-          }
           uint32_t v[32];
           tmem_ld32(taddr + pn * 64 + eg * 32, v);
           tmem_ld_wait();
-          if (KIND == DGRAD && fuse_add) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint32_t ww[4] = {addv[q].x, addv[q].y, addv[q].z, addv[q].w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float lo = __uint_as_float(ww[e] << 16), hi = __uint_as_float(ww[e] & 0xffff0000u);
-                const int j = 8 * q + 2 * e;
-                v[j] = ((mbits >> j) & 1u) ? __float_as_uint(__uint_as_float(v[j]) + lo) : 0u;
-                v[j + 1] = ((mbits >> (j + 1)) & 1u) ? __float_as_uint(__uint_as_float(v[j + 1]) + hi) : 0u;
-              }
-            }
-          }
           if (p.bias) {
             const int col = it.n0 + pn * 64 + eg * 32;
 #pragma unroll
@@ -907,10 +1061,12 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
             o[q].w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
           }
           // the panel buffer is needed only now: its previous TMA store has finished reading it ...
-          if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
-          if (KIND != WGRAD && with_stats)   // ... and so have the statistics warps
-            asm volatile("bar.sync %0, %1;" ::"r"(6 + (P == 1 ? bsel : (pn + P - 2) % P)), "n"(CNT) : "memory");
+          if (!fan) {
+            if (store_thread) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
+          }
+          if (KIND != WGRAD && with_stats)   // ... and so have the statistics warps (fan-in mode: they own the store)
+            asm volatile("bar.sync %0, %1;" ::"r"(6 + (P == 1 ? bsel : (pn + P - 2) % P)), "r"(free_cnt) : "memory");
           uint8_t* prow = buf + row * 128;
 #pragma unroll
           for (int q = 0; q < 4; ++q)  // 16-byte chunk eg*4+q of the 128-byte panel row, XOR-swizzled by the row phase
@@ -918,12 +1074,14 @@ __global__ void __launch_bounds__(KIND != WGRAD ? kThreads2 + 32 * kStatWarps2<B
           fence_proxy_async_smem();
           if (with_stats) {                                  // panel complete: hand it to the statistics warps
             __threadfence_block();
-            asm volatile("bar.arrive %0, %1;" ::"r"(2 + (P == 1 ? bsel : pn)), "n"(CNT) : "memory");
+            asm volatile("bar.arrive %0, %1;" ::"r"(2 + (P == 1 ? bsel : pn)), "r"(full_cnt) : "memory");
           }
-          asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
-          if (store_thread) {
-            tma_store_2d(buf, &tmC, it.n0 + pn * 64, it.m0);
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (!fan) {
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads2) : "memory");
+            if (store_thread) {
+              tma_store_2d(buf, &tmC, it.n0 + pn * 64, it.m0);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
           }
         }
       } else if (KIND != WGRAD) {
@@ -1281,7 +1439,7 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int KIND, int AMODE, int BN, int MT = 1>
+template <int KIND, int AMODE, int BN, int MT = 1, int FAN = 0>
 static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p_in, int items,
                            cudaStream_t st) {
   ConvParams p = p_in;
@@ -1291,7 +1449,7 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     int e = make_tmap_2d_bf16(&tmC, p.out, (uint64_t)p.Ncols, (uint64_t)p.M, 64, 128);
     if (e) return (cudaError_t)e;
   }
-  auto kern = igemm2_kernel<KIND, AMODE, BN, MT>;
+  auto kern = igemm2_kernel<KIND, AMODE, BN, MT, FAN>;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN, MT>::kSmem);
@@ -1299,7 +1457,8 @@ static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const
     configured = true;
   }
   const int grid = items < num_sms() ? items : num_sms();
-  const int threads = (KIND != WGRAD && p.stats) ? kThreads2 + 32 * kStatWarps2<BN> : (KIND == WGRAD ? kThreads2W : kThreads2);
+  const int threads = (KIND != WGRAD && (p.stats || FAN)) ? kThreads2 + 32 * kStatWarps2<BN> + (FAN ? 32 : 0)
+                                                  : (KIND == WGRAD ? kThreads2W : kThreads2);
   kern<<<grid, threads, Cfg2<BN, MT>::kSmem, st>>>(tmA, tmB, tmC, p, items);
   return cudaGetLastError();
 }
@@ -1514,16 +1673,22 @@ extern "C" int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int
   return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, nullptr, nullptr, stream);
 }
 
-// dx = mask ? (dgrad + add) : 0 in the epilogue (add: bf16 [N,H,W,Cin]; mask: 1 bit per element, optional).
-// Returns -1 (nothing launched) when the active kernel variant cannot fuse it: the caller then runs the plain dgrad
-// and its own add / mask pass.
+// Residual fan-in fused into dgrad: dx = mask ? (dgrad + add) : 0 (add: bf16 NHWC like dx; mask: 1 bit per element,
+// nullable), computed by the statistics warps on the bf16 panel in shared memory, together with the BatchNorm-backward
+// sums of dx (as b2_conv_dgrad_bnstats, with g = dx already masked). Returns -1 (nothing launched) when the active
+// kernel variant cannot do it: the caller then runs the plain dgrad and the two-input BatchNorm backward.
 extern "C" int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
                                    int KH, int KW, int stride, int pad, const void* add, const void* mask,
+                                   const void* bn_y, const float* bn_mean, float* partial, int* blocks,
                                    void* stream) {
-  if (!add) return cudaErrorInvalidValue;
-  const bool v2_tma_epilogue = g_impl == 2 && stride == 1 && pick_mode(DGRAD, KH, KW, stride, pad) != ACT_GATHER;
-  if (!v2_tma_epilogue) return -1;
-  return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, add, mask, stream);
+  if (!add || !blocks || (bn_y && (!bn_mean || !partial))) return cudaErrorInvalidValue;
+  *blocks = 0;
+  const int bn = bn_for(Cin);
+  const bool ok = g_impl == 2 && g_fuse_stats && stride == 1 && Cin % 64 == 0 && Cin % bn == 0 &&
+                  pick_mode(DGRAD, KH, KW, stride, pad) != ACT_GATHER;
+  if (!ok) return -1;
+  DgradBn req{bn_y, nullptr, bn_mean, partial, blocks};
+  return conv_dgrad_impl(dy, w, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, add, mask, stream, &req);
 }
 
 // dgrad that also leaves the partial sums of the BatchNorm backward of dx behind (dx is the gradient of that
@@ -1589,7 +1754,19 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
       p.bwd_y = (const __nv_bfloat16*)bnreq->y;
       p.bwd_mask = (const unsigned char*)bnreq->mask;
       p.bwd_mean = bnreq->mean;
-      *bnreq->blocks = (bn == 256 ? 1 : 2) * grid;
+      p.fanin = add ? 1 : 0;
+      if (!bnreq->y) p.stats = nullptr;    // fan-in only, no BatchNorm-backward sums
+      *bnreq->blocks = !bnreq->y ? 0 : (add ? (bn == 64 ? 2 : 4) : (bn == 256 ? 1 : 2)) * grid;
+    }
+    if (p.fanin) {
+      if (mode == ACT_TILED) {
+        if (bn == 256) return launch2<DGRAD, ACT_TILED, 256, 1, 1>(tmA, tmB, p, items, st);
+        if (bn == 128) return launch2<DGRAD, ACT_TILED, 128, 1, 1>(tmA, tmB, p, items, st);
+        return launch2<DGRAD, ACT_TILED, 64, 1, 1>(tmA, tmB, p, items, st);
+      }
+      if (bn == 256) return launch2<DGRAD, ACT_IM2COL, 256, 1, 1>(tmA, tmB, p, items, st);
+      if (bn == 128) return launch2<DGRAD, ACT_IM2COL, 128, 1, 1>(tmA, tmB, p, items, st);
+      return launch2<DGRAD, ACT_IM2COL, 64, 1, 1>(tmA, tmB, p, items, st);
     }
     return launch2_mode<DGRAD>(mode, bn, tmA, tmB, p, items, st);
   }

@@ -61,11 +61,14 @@ int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, 
 int b2_conv_dgrad_bnstats(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
                           int KW, int stride, int pad, const void* bn_y, const void* bn_mask, const float* bn_mean,
                           float* partial, int* blocks, void* stream);
-/* dgrad with the gradient fan-in and the ReLU backward fused into the epilogue: dx = mask ? (dgrad + add) : 0
- * (add: bf16 NHWC like dx; mask: 1 bit per element as written by b2_bn_fwd_train, nullable). Returns -1 without
- * launching anything when the active kernel variant cannot fuse it. */
+/* dgrad with the residual fan-in fused: dx = mask ? (dgrad + add) : 0 (add: bf16 NHWC like dx; mask: 1 bit per
+ * element as written by b2_bn_fwd_train, nullable), done by the statistics warps on the output panel in shared memory,
+ * which also produce the BatchNorm-backward sums of dx against bn_y / bn_mean (as b2_conv_dgrad_bnstats; dx is already
+ * masked, so hand it to b2_bn_bwd_partial with relu = 0). Returns -1 without launching anything when the active
+ * kernel variant cannot do it. */
 int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH,
-                        int KW, int stride, int pad, const void* add, const void* mask, void* stream);
+                        int KW, int stride, int pad, const void* add, const void* mask, const void* bn_y,
+                        const float* bn_mean, float* partial, int* blocks, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.
  * accumulate != 0 adds into dw (gradient accumulation / no_sync), otherwise dw is overwritten. */
 int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N, int H, int W,

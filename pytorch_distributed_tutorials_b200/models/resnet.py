@@ -215,9 +215,11 @@ class ResNetEngine:
         self.stem_wp_direct = torch.zeros(64, 224, dtype=torch.bfloat16, device=self.device)
         # direct stem (no im2col matrix); B200DDP_STEM=im2col selects the materialised-im2col GEMM path instead
         self.stem_direct = os.environ.get("B200DDP_STEM", "direct") != "im2col"
-        # fuse the residual fan-in add + ReLU backward into the first conv's dgrad epilogue. Off by default: the
-        # epilogue's row-per-thread reads of the skip gradient cost more than the BatchNorm-backward bytes they save
-        # (measured: R50 bs256 dgrad +3.0 ms vs BN reduce -1.2 ms).
+        # B200DDP_FUSE_FANIN=1: the first conv's dgrad of every block also finishes the residual fan-in (skip gradient
+        # add + ReLU backward of the block input, done by the kernel's statistics warps on the output panel in shared
+        # memory) and produces the previous block's BatchNorm-backward sums. Correct (tests) but off by default: the
+        # panel hand-offs (epilogue -> statistics warps -> store warp, two panel buffers) leave the kernel at
+        # ~3 TB/s, 0.44 ms on the 256-channel 56x56 layer against 0.09 + 0.27 ms for dgrad + the two-input reduce pass.
         self.fuse_fanin = os.environ.get("B200DDP_FUSE_FANIN", "0") == "1"
         # the dgrad that produces a BatchNorm's output gradient also produces that BatchNorm's backward sums
         self.fuse_bn_bwd = os.environ.get("B200DDP_FUSE_BN_BWD", "1") != "0"
@@ -367,15 +369,17 @@ class ResNetEngine:
         writer(out, False)
         return out
 
-    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, dx_add=None, dx_mask=None,
+    def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, fan=None,
                   given_blocks=0, next_rec=None):
         """Backward of one conv+BN(+ReLU) unit. ``pre_masked``: dz_a already is the complete, ReLU-masked gradient
-        of this unit's output (produced by a fused dgrad epilogue), so it doubles as the residual-branch gradient.
-        ``dx_add`` / ``dx_mask``: fan-in gradient (and the ReLU mask of this unit's input) to fuse into the dgrad
-        epilogue; the returned flag says whether that happened. ``given_blocks`` > 0: the dgrad that produced dz_a
-        already left this BatchNorm's backward sums in ``native.bn_partial_b`` (the reduce pass is skipped).
-        ``next_rec``: the unit whose BatchNorm consumes this unit's dx - its backward sums are produced by this
-        unit's dgrad and the block count is left in ``self._bn_blocks``."""
+        of this unit's output (produced by a fan-in dgrad), so it doubles as the residual-branch gradient.
+        ``fan`` = (skip gradient, record of the previous block's last unit): fuse the residual fan-in, the ReLU
+        backward of this unit's input and the previous block's BatchNorm-backward sums into this unit's dgrad; the
+        second return value then is the number of partial rows produced (0: not fused, plain dgrad returned).
+        ``given_blocks`` > 0: the dgrad that produced dz_a already left this BatchNorm's backward sums in
+        ``native.bn_partial_b`` (the reduce pass is skipped). ``next_rec``: the unit whose BatchNorm consumes this
+        unit's dx - its backward sums are produced by this unit's dgrad, the block count is left in
+        ``self._bn_blocks``."""
         conv, bn = rec.conv, rec.bn
         st = self._bn(bn)
         # BN backward needs dgamma/dbeta destinations up front (the finalize kernel writes them).
@@ -383,10 +387,10 @@ class ResNetEngine:
         db_slot = self._slot(bn.bias)
         if given_blocks > 0:
             dy = native.bn_bwd_partial(dz_a, rec.y, bn.weight, st.mean, st.invstd, dg_slot[0], db_slot[0],
-                                       dg_slot[1] and db_slot[1], rec.relu, st.coef,
+                                       dg_slot[1] and db_slot[1], rec.relu and not pre_masked, st.coef,
                                        native.bn_partial_b(self.device), given_blocks,
-                                       self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
-            dres = None
+                                       self._sync_bn_ctx(bn), self.xg_slot, None if pre_masked else rec.mask)
+            dres = dz_a if pre_masked else None
         elif pre_masked:
             dy, _ = native.bn_bwd(dz_a, None, None, rec.y, bn.weight, st.mean, st.invstd,
                                   dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], False, st.coef, False,
@@ -413,10 +417,11 @@ class ResNetEngine:
         s, pd = conv.stride[0], conv.padding[0]
         # dgrad first: delivering the weight gradient may complete a bucket, and the fused all-reduce + SGD kernel
         # that this triggers rewrites the bucket's weights — every reader of the old weights must already be queued
-        dx, fused = None, False
-        if need_dx and dx_add is not None:
-            dx = convops.conv_dgrad_fused(dy, self._w16(w), rec.x.shape, s, pd, dx_add, dx_mask)
-            fused = dx is not None
+        dx, fan_blocks = None, 0
+        if need_dx and fan is not None:
+            skip, prev = fan
+            dx, fan_blocks = convops.conv_dgrad_fused(dy, self._w16(w), rec.x.shape, s, pd, skip, prev.mask, prev.y,
+                                                      self._bn(prev.bn).mean, native.bn_partial_b(self.device))
         self._bn_blocks = 0
         if need_dx and dx is None and next_rec is not None and self.fuse_bn_bwd and next_rec.relu:
             nst = self._bn(next_rec.bn)
@@ -427,8 +432,8 @@ class ResNetEngine:
             dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd)
         g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
         grads[id(w)] = g
-        if dx_add is not None:
-            return dx, fused
+        if fan is not None:
+            return dx, fan_blocks
         return dx, dres
 
     def _slot(self, p):
@@ -459,7 +464,7 @@ class ResNetEngine:
         grads[id(m.fc.weight)] = self._deliver(m.fc.weight, lambda out, acc: convops.gemm_tn(dl, pooled, out, acc))
         da, db = native.avgpool_bwd(dpooled, feat_shape), None
         rev = list(reversed(block_tapes))
-        pre_masked = False
+        pre_blocks = 0       # > 0: da is the finished fan-in gradient of the block output, sums are in bn_partial_b
         for i, (blk, bt) in enumerate(rev):
             n_main = len(blk.units())
             recs_main = bt[:n_main - 1]
@@ -467,29 +472,27 @@ class ResNetEngine:
             rec_last = bt[-1]
             # each dgrad of the main path also produces the BatchNorm-backward sums of the unit it feeds
             chain = list(recs_main)            # first .. last-but-one unit of the main path
-            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_masked,
-                                     next_rec=chain[-1])
+            d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_blocks > 0,
+                                     given_blocks=pre_blocks, next_rec=chain[-1])
             blocks_first = self._bn_blocks
             for j in range(len(chain) - 1, 0, -1):
                 d, _ = self._unit_bwd(chain[j], d, None, True, False, grads, given_blocks=self._bn_blocks,
                                       next_rec=chain[j - 1])
                 blocks_first = self._bn_blocks
             # gradient of the block input = dgrad(first conv) + skip-path gradient, masked by the ReLU that produced
-            # the input (the previous block's output ReLU): both fused into the first conv's dgrad epilogue
+            # the input (the previous block's output ReLU): finished inside the first conv's dgrad kernel, which
+            # also produces the BatchNorm-backward sums of the previous block's last unit
             skip = dres
             if rec_ds is not None:
                 skip, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
-            prev_mask = rev[i + 1][1][-1].mask if i + 1 < len(rev) else None
-            if self.fuse_fanin:
-                d, fused = self._unit_bwd(recs_main[0], d, None, True, False, grads, dx_add=skip, dx_mask=prev_mask,
-                                          given_blocks=blocks_first)
+            prev_last = rev[i + 1][1][-1] if i + 1 < len(rev) else None
+            pre_blocks = 0
+            if self.fuse_fanin and prev_last is not None and prev_last.relu and prev_last.mask is not None:
+                d, pre_blocks = self._unit_bwd(recs_main[0], d, None, True, False, grads, fan=(skip, prev_last),
+                                               given_blocks=blocks_first)
             else:
-                (d, _), fused = self._unit_bwd(recs_main[0], d, None, True, False, grads,
-                                               given_blocks=blocks_first), False
-            if fused:
-                da, db, pre_masked = d, None, prev_mask is not None
-            else:
-                da, db, pre_masked = d, skip, False
+                d, _ = self._unit_bwd(recs_main[0], d, None, True, False, grads, given_blocks=blocks_first)
+            da, db = (d, None) if pre_blocks > 0 else (d, skip)
         dz = native.maxpool_bwd(pool_idx, stem_shape, da, db)
         self._unit_bwd(tape[0], dz, None, False, False, grads)
         return grads

@@ -116,20 +116,25 @@ def gemm_nt_stats(a, w, partial):
     return y, blocks.value
 
 
-def conv_dgrad_fused(dy, w, x_shape, stride, pad, add, mask=None):
-    """dx = mask ? (dgrad + add) : 0 with the add / ReLU-mask applied in the dgrad epilogue. Returns None when the
-    active kernel variant cannot fuse it (the caller then falls back to conv_dgrad plus its own fan-in)."""
+def conv_dgrad_fused(dy, w, x_shape, stride, pad, add, mask, bn_y, bn_mean, partial):
+    """Residual fan-in fused into dgrad: dx = mask ? (dgrad + add) : 0, finished by the kernel's statistics warps on
+    the output panel in shared memory, which also leave the BatchNorm-backward sums of dx (against bn_y / bn_mean) in
+    ``partial`` (bn_y None: fan-in only, blocks = 0). Returns (dx, blocks), or (None, 0) when the active kernel
+    variant cannot do it."""
     N, Cin, H, W = x_shape
     Cout, _, KH, KW = w.shape
     assert _is_cl(dy) and _is_cl(w) and _is_cl(add) and tuple(add.shape) == tuple(x_shape)
+    assert bn_y is None or (_is_cl(bn_y) and tuple(bn_y.shape) == tuple(x_shape))
     dx = torch.empty((N, Cin, H, W), dtype=torch.bfloat16, device=dy.device, memory_format=torch.channels_last)
+    blocks = ctypes.c_int(0)
     e = _lib.lib().b2_conv_dgrad_fused(_lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), N, H, W, Cin, Cout, KH, KW, stride,
-                                       pad, _lib.ptr(add), _lib.ptr(mask), _lib.stream_ptr())
+                                       pad, _lib.ptr(add), _lib.ptr(mask), _lib.ptr(bn_y), _lib.ptr(bn_mean),
+                                       _lib.ptr(partial), ctypes.byref(blocks), _lib.stream_ptr())
     if e == -1:
-        return None
+        return None, 0
     _lib.check(e, "b2_conv_dgrad_fused")
     _lib.count_launch()
-    return dx
+    return dx, blocks.value
 
 
 def conv_dgrad_bnstats(dy, w, x_shape, stride, pad, bn_y, bn_mask, bn_mean, partial):

@@ -263,25 +263,38 @@ def test_direct_stem_conv(N, H, W):
     assert _rel(dw.permute(0, 3, 1, 2), 2 * ref_dw) < 5e-3
 
 
-@pytest.mark.parametrize("ci,co,k,p,H,N", [(256, 64, 1, 0, 28, 4), (64, 64, 3, 1, 14, 3), (512, 128, 1, 0, 7, 5)])
-def test_conv_dgrad_epilogue_fan_in_and_relu_mask(ci, co, k, p, H, N):
-    """dx = mask ? (dgrad + add) : 0 applied in the dgrad epilogue (residual fan-in + ReLU backward)."""
-    from pytorch_distributed_tutorials_b200.ops import conv
+@pytest.mark.parametrize("ci,co,k,p,H,N", [(256, 64, 1, 0, 28, 4), (64, 64, 3, 1, 14, 3), (512, 128, 1, 0, 7, 5),
+                                            (128, 64, 1, 0, 28, 3), (1024, 256, 1, 0, 14, 6)])
+def test_conv_dgrad_fan_in_relu_mask_and_bn_backward_sums(ci, co, k, p, H, N):
+    """dx = mask ? (dgrad + add) : 0 finished by the statistics warps (residual fan-in + ReLU backward), which also
+    leave sum(dx), sum(dx * (y - mean)) per channel."""
+    from pytorch_distributed_tutorials_b200.ops import conv, native
     torch.manual_seed(5)
     w = _bf(torch.randn(co, ci, k, k, device=DEV) / (ci * k * k) ** 0.5)
     dy = _bf(torch.randn(N, co, H, H, device=DEV))
     add = _bf(torch.randn(N, ci, H, H, device=DEV))
+    y = _bf(torch.randn(N, ci, H, H, device=DEV))
+    mean = torch.randn(ci, device=DEV) * 0.1
     keep = torch.rand(N, H, H, ci, device=DEV) > 0.4                     # NHWC, as the mask is laid out
     bits = (keep.view(N, H, H, ci // 8, 8).to(torch.uint8) << torch.arange(8, device=DEV, dtype=torch.uint8)).sum(
         -1).to(torch.uint8)
-    got = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, bits)
-    assert got is not None
-    ref = conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p) + add.float()
-    ref = torch.where(keep.permute(0, 3, 1, 2), ref, torch.zeros_like(ref))
-    assert _rel(got, ref) < 1e-2
-    assert (got.float()[~keep.permute(0, 3, 1, 2)] == 0).all()
-    got2 = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, None)
-    assert _rel(got2, conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p) + add.float()) < 1e-2
+    partial = native.bn_partial_b(torch.device(DEV))
+    for mask, keep_nchw in ((bits, keep.permute(0, 3, 1, 2)), (None, None)):
+        partial.fill_(float("nan"))
+        got, blocks = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, mask, y, mean, partial)
+        torch.cuda.synchronize()
+        assert got is not None and blocks > 0
+        # the kernel rounds the dgrad to bf16 before the add (as the unfused path does)
+        ref = conv.ref_dgrad(dy.float(), w.float(), (N, ci, H, H), 1, p).to(torch.bfloat16).float() + add.float()
+        if keep_nchw is not None:
+            ref = torch.where(keep_nchw, ref, torch.zeros_like(ref))
+            assert (got.float()[~keep_nchw] == 0).all()
+        assert _rel(got, ref) < 1.5e-2
+        part = partial[: blocks * 2 * ci].view(blocks, 2, ci).sum(0)
+        g = got.float()
+        ref0, ref1 = g.sum((0, 2, 3)), (g * (y.float() - mean.view(1, -1, 1, 1))).sum((0, 2, 3))
+        assert torch.allclose(part[0], ref0, rtol=1e-3, atol=5e-2), (part[0] - ref0).abs().max()
+        assert torch.allclose(part[1], ref1, rtol=1e-3, atol=5e-2), (part[1] - ref1).abs().max()
 
 
 @pytest.mark.parametrize("ci,co,k,p,H,N", [(64, 256, 1, 0, 28, 4), (128, 128, 3, 1, 14, 3), (256, 1024, 1, 0, 14, 5),
