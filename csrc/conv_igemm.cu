@@ -439,6 +439,7 @@ static int pick_bn(int ncols, int force) {
 static int g_force_bn = 0;
 static int g_dbg = 0;
 static int g_mt2 = 1;     // v2 wgrad: 256 x 256 tile per CTA where Cout allows (b2_conv_set_wgrad_mt2)
+static int g_wgrad_waves = 1;   // v2 wgrad split-K target: work items per SM (1: half the partial-sum traffic of 2)
 static int g_panels = 1;  // v2: fetch MN-major operands as one multi-panel TMA box (b2_conv_set_panels)
 static int g_act_mode = -1;  // -1 auto, else force ACT_GATHER / ACT_IM2COL for k>1 or strided convs
 
@@ -1526,6 +1527,7 @@ extern "C" void b2_conv_set_act_mode(int mode) { g_act_mode = mode; }
 extern "C" void b2_conv_set_debug(int bits) { g_dbg = bits; }
 extern "C" void b2_conv_set_panels(int on) { g_panels = on; }
 extern "C" void b2_conv_set_wgrad_mt2(int on) { g_mt2 = on; }
+extern "C" void b2_conv_set_wgrad_waves(int n) { g_wgrad_waves = n; }
 
 extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
 
@@ -1787,6 +1789,7 @@ extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, in
   const long long tiles = flat ? (long long)((Cout + BM - 1) / BM) * ((taps * Cin + 255) / 256)
                                : (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
   long long want = ((g_impl >= 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
+  if (g_impl == 2 && g_wgrad_waves == 1 && tiles <= 148) want = 148 / tiles;   // one item per SM, single wave
   if (wgrad_mt2(bn, Cout)) {   // half as many (256-row) tiles, one item per SM in a single wave
     const long long t2 = tiles / 2;
     want = 148 / t2;

@@ -52,6 +52,8 @@ void b2_conv_set_debug(int bits);
 void b2_conv_set_panels(int on);
 /* 1 (default): wgrad with Cout % 256 == 0 computes one 256 x 256 tile per CTA (all 512 TMEM columns) */
 void b2_conv_set_wgrad_mt2(int on);
+/* split-K target of the 128-row wgrad tiles: work items per SM (1 = default: fewer, longer splits; 2) */
+void b2_conv_set_wgrad_waves(int n);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* dgrad that also produces the partial sums of the BatchNorm backward whose output gradient it computes (statistics

@@ -19,7 +19,11 @@ def main():
     ap.add_argument("--image-size", type=int, default=224)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--rows", type=int, default=40)
+    ap.add_argument("--wgrad-waves", type=int, default=0, help="experiment: split-K items per SM of the wgrad kernels")
     a = ap.parse_args()
+    if a.wgrad_waves:
+        from pytorch_distributed_tutorials_b200.ops import _lib
+        _lib.lib().b2_conv_set_wgrad_waves(a.wgrad_waves)
     args = argparse.Namespace(model=a.model, batch=a.batch, image_size=a.image_size, sync_bn=False,
                               bucket_cap_mb=None, no_fuse_optimizer=False, ref_variant="r1", no_graph=True)
     torch.cuda.set_device(0)
