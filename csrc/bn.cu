@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
   (void)rows_per_blk;
   if (r < RP) {
     Vec8 mu = load_f32x8(mean + cv * 8);
-#pragma unroll 2
+#pragma unroll 4
     for (long long row = (long long)blockIdx.x * RP + r; row < M; row += (long long)gridDim.x * RP) {
       const long long off = row * C + cv * 8;
       Vec8 g = load_bf16x8(dza + off);
