@@ -34,7 +34,8 @@ typedef struct b2_xgpu_ctx {
  * Reference: resnet/main.py:76,121,123 (torchvision resnet -> cuDNN fprop / dgrad / wgrad).
  * x: NHWC bf16 [N,H,W,Cin]; w: OHWI bf16 [Cout,KH,KW,Cin]; y: NHWC bf16 [N,Ho,Wo,Cout]; dw: OHWI fp32.
  * Cin must be a multiple of 64 and Cout of 8 (the classifier runs as a 1x1 conv with Cout=1000; the 3-channel
- * stem goes through b2_stem_im2col and then these same kernels with Cin=192).
+ * stem has its own kernels, b2_stem_fprop / b2_stem_wgrad, or, for outputs wider than 112 pixels, goes through
+ * b2_stem_im2col and then these same kernels with Cin=192).
  * ---------------------------------------------------------------------------------------------- */
 int b2_conv_fprop(const void* x, const void* w, const float* bias /*nullable, fp32[Cout]*/, void* y, int N, int H,
                   int W, int Cin, int Cout, int KH, int KW, int stride, int pad, void* stream);
