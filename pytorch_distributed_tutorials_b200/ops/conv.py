@@ -138,7 +138,8 @@ def conv_dgrad_fused(dy, w, x_shape, stride, pad, add, mask, bn_y, bn_mean, part
 
 
 def conv_dgrad_bnstats(dy, w, x_shape, stride, pad, bn_y, bn_mask, bn_mean, partial):
-    """conv_dgrad whose statistics warps also produce the reduce pass of the BatchNorm backward that consumes dx
+    """conv_dgrad (cuDNN dgrad in the reference's loss.backward(), resnet/main.py:123) whose statistics warps also
+    produce the reduce pass of the BatchNorm backward that consumes dx
     (dx = gradient of relu(bn(bn_y))). Returns (dx, blocks); blocks == 0: not produced, run the normal bn_bwd."""
     N, Cin, H, W = x_shape
     Cout, _, KH, KW = w.shape

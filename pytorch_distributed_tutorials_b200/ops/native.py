@@ -87,7 +87,8 @@ def bn_partial_b(device):
 
 def bn_bwd_partial(dz, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, partial, partial_blocks,
                    xg=None, xg_slot=0, mask=None):
-    """bn_bwd for a single incoming gradient whose reduce pass was done by the dgrad that produced it."""
+    """bn_bwd for a single incoming gradient whose reduce pass was done by the dgrad that produced it
+    (native_batch_norm_backward inside loss.backward(), reference resnet/main.py:123)."""
     M, C = _mc(y)
     dy = torch.empty_like(y)
     e = _lib.lib().b2_bn_bwd_partial(ptr(dz), None, ptr(mask), ptr(y), ptr(dy), c_ll(M), C, ptr(gamma), ptr(mean),
@@ -225,7 +226,8 @@ def stem_supported(h, w):
 
 
 def stem_pack_input(x):
-    """[N,3,H,W] fp32/bf16 NCHW -> zero-padded NHWC4 bf16 image (flat) for the direct stem kernels."""
+    """[N,3,H,W] fp32/bf16 NCHW -> zero-padded NHWC4 bf16 image (flat) for the direct stem kernels
+    (the 7x7/2 conv1 of the torchvision ResNet the reference builds at resnet/main.py:76)."""
     n, c, h, w = x.shape
     assert c == 3 and x.is_contiguous()
     lib = _lib.lib()
@@ -245,7 +247,8 @@ def stem_pack_weight(w_ohwi_fp32, out):
 
 
 def stem_fprop(xp, wp, n, h, w, partial=None):
-    """7x7/2 stem convolution from the padded image. Returns (y [N,64,Ho,Wo] channels_last bf16, stats blocks)."""
+    """7x7/2 stem convolution from the padded image (forward of reference resnet/main.py:121 for conv1).
+    Returns (y [N,64,Ho,Wo] channels_last bf16, stats blocks)."""
     ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
     y = torch.empty((n, 64, ho, wo), dtype=torch.bfloat16, device=xp.device, memory_format=torch.channels_last)
     blocks = ctypes.c_int(0)
@@ -257,7 +260,8 @@ def stem_fprop(xp, wp, n, h, w, partial=None):
 
 
 def stem_wgrad(xp, dy, dw, n, h, w, accumulate):
-    """dW (fp32 OHWI [64,7,7,3], written or accumulated) of the stem from the padded image and dy (NHWC bf16)."""
+    """dW (fp32 OHWI [64,7,7,3], written or accumulated) of the stem from the padded image and dy (NHWC bf16):
+    conv1's share of loss.backward(), reference resnet/main.py:123."""
     lib = _lib.lib()
     lib.b2_stem_wgrad_workspace_floats.restype = ctypes.c_longlong
     ws = scratch(xp.device, "stem_wgrad_ws", lib.b2_stem_wgrad_workspace_floats())
