@@ -295,6 +295,9 @@ def test_conv_dgrad_fan_in_relu_mask_and_bn_backward_sums(ci, co, k, p, H, N):
         ref0, ref1 = g.sum((0, 2, 3)), (g * (y.float() - mean.view(1, -1, 1, 1))).sum((0, 2, 3))
         assert torch.allclose(part[0], ref0, rtol=1e-3, atol=5e-2), (part[0] - ref0).abs().max()
         assert torch.allclose(part[1], ref1, rtol=1e-3, atol=5e-2), (part[1] - ref1).abs().max()
+        # fan-in only (no BatchNorm sums): same dx, bit for bit
+        got0, blocks0 = conv.conv_dgrad_fused(dy, w, (N, ci, H, H), 1, p, add, mask, None, None, None)
+        assert got0 is not None and blocks0 == 0 and torch.equal(got0, got)
 
 
 @pytest.mark.parametrize("ci,co,k,p,H,N", [(64, 256, 1, 0, 28, 4), (128, 128, 3, 1, 14, 3), (256, 1024, 1, 0, 14, 5),
