@@ -193,3 +193,30 @@ def test_fused_reduce_update_equals_update_in_step():
         results.append([p.detach().clone() for p in ddp.parameters()])
         assert len(ddp.store.buckets) > 10
     assert all(torch.equal(a, b) for a, b in zip(*results))
+
+
+@pytest.mark.parametrize("name", ["resnet18", "resnet50"])
+def test_engine_delivers_gradients_in_the_planned_order(name):
+    """DDP plans its buckets from ``grad_ready_order()``; the engine's backward must produce the gradients in
+    exactly that order (buckets then fill front to back and the reductions overlap with the rest of backward)."""
+    torch.manual_seed(0)
+    m = _build(name).to(DEV)
+    x = torch.randn(4, 3, 64, 64, device=DEV)
+    m(x)                                                  # builds the engine lazily
+    eng = m._engine
+    assert eng is not None
+    seen = []
+    orig_publish, orig_deliver = eng._publish, eng._deliver
+
+    def publish(p, slot, grads):
+        seen.append(id(p))
+        return orig_publish(p, slot, grads)
+
+    def deliver(p, writer):
+        seen.append(id(p))
+        return orig_deliver(p, writer)
+
+    eng._publish, eng._deliver = publish, deliver
+    m(x).sum().backward()
+    planned = [id(p) for p in m.grad_ready_order()]
+    assert seen == planned
