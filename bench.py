@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--no-fuse-optimizer", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying "
                     "the captured whole-step CUDA graph")
+    ap.add_argument("--no-comm-probe", action="store_true", help="skip the backward with/without-sync probe")
     ap.add_argument("--reference-strict", action="store_true",
                     help="report the reference as unavailable instead of running the minimally-fixed harness")
     return ap.parse_args()
@@ -58,19 +59,30 @@ def dist_setup():
     return rank, local_rank, world
 
 
+_CPU_PLANE = False   # ours arm: the process group is gloo only (no NCCL communicator exists in the process)
+
+
 def barrier_sync(world):
     torch.cuda.synchronize()
     if world > 1:
-        dist.barrier()
+        dist.barrier()          # gloo (CPU) for our arm, NCCL for the reference arm
     torch.cuda.synchronize()
 
 
 def max_over_ranks(v, world):
     if world == 1:
         return v
-    t = torch.tensor([v], dtype=torch.float64, device="cuda")
+    t = torch.tensor([v], dtype=torch.float64, device="cpu" if _CPU_PLANE else "cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def gather_objects(obj, world):
+    if world == 1:
+        return [obj]
+    out = [None] * world
+    dist.all_gather_object(out, obj)
+    return out
 
 
 def timed_region(step_fn, steps, world):
@@ -118,9 +130,14 @@ def build_ours(args, local_rank, world):
     from pytorch_distributed_tutorials_b200.parallel import (DistributedDataParallel, convert_sync_batchnorm,
                                                              init_process_group)
     from pytorch_distributed_tutorials_b200.utils.seed import set_random_seeds
+    global _CPU_PLANE
     set_random_seeds(0)
     if world > 1:
-        init_process_group(backend="b200", local_rank=local_rank)
+        init_process_group(backend="b200", local_rank=local_rank)   # gloo control plane only; pins CPU/NUMA
+        _CPU_PLANE = True
+    else:
+        from pytorch_distributed_tutorials_b200.utils.affinity import pin_to_gpu_numa_node
+        pin_to_gpu_numa_node(local_rank)
     dev = torch.device("cuda", local_rank)
     model = MODELS[args.model]()
     if args.sync_bn:
@@ -128,6 +145,10 @@ def build_ours(args, local_rank, world):
     model = model.to(dev)
     ddp = DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank,
                                   bucket_cap_mb=args.bucket_cap_mb)
+    if world > 1:
+        # the product path or nothing: a silent fallback to torch collectives would still print a number
+        assert ddp.backend == "p2p", "expected the peer-memory backend, got %r" % ddp.backend
+        ddp.comm.set_spin_timeout_ms(120000)   # a benchmark has no rank-0-only phases: fail fast on a lost peer
     opt = optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-5,
                     fuse_with_backward=not args.no_fuse_optimizer)
     crit = CrossEntropyLoss()
@@ -137,7 +158,45 @@ def build_ours(args, local_rank, world):
     # the fused SGD epilogue) -> step, captured into one CUDA graph after three eager steps
     step = GraphedTrainStep(ddp, crit, opt, warmup=3, enabled=not args.no_graph)
     ddp._bench_step = step
+    ddp._bench_parts = (crit, opt, lambda x: x)
     return step, ddp
+
+
+def replica_checksum(ddp):
+    """Bit-level checksum of this rank's flat fp32 parameters (wrapping int64 sum of the raw words)."""
+    tot = 0
+    for b in ddp.store.buckets:
+        tot += int(b.p32.view(torch.int32).sum(dtype=torch.int64).item())
+    return tot & 0xFFFFFFFFFFFFFFFF
+
+
+def backward_comm_overhead(ddp, parts, x, y, world, autocast, n=3):
+    """How much longer ``loss.backward()`` takes WITH gradient synchronisation than without (``no_sync()``), by
+    CUDA events, eager launches, mean over ``n`` pairs, max over ranks. Same probe for both arms: it contains the
+    exposed tail of the last reduction AND whatever the reductions cost backward's own kernels (SM / bandwidth
+    contention) - the cross-check SURVEY 7.3 #9 asks for beside the tail measured with device timestamps."""
+    if world == 1:
+        return 0.0
+    import contextlib
+    crit, opt, prep = parts
+    times = {True: [], False: []}
+    for i in range(2 * n + 2):
+        sync = (i % 2 == 0)
+        opt.zero_grad()
+        with (contextlib.nullcontext() if sync else ddp.no_sync()):
+            with (torch.autocast("cuda", dtype=torch.bfloat16) if autocast else contextlib.nullcontext()):
+                loss = crit(ddp(prep(x)), y)
+            barrier_sync(world)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            loss.backward()
+            e1.record()
+            e1.synchronize()
+        opt.step()
+        if i >= 2:
+            times[sync].append(e0.elapsed_time(e1))
+    d = sum(times[True]) / len(times[True]) - sum(times[False]) / len(times[False])
+    return max_over_ranks(max(0.0, d), world)
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
@@ -198,6 +257,8 @@ def build_reference(args, local_rank, world):
     crit = nn.CrossEntropyLoss()
     opt = optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-5, **({"fused": True} if r1 else {}))
     ddp.train()
+    ddp._bench_parts = (crit, opt, (lambda x: x.contiguous(memory_format=torch.channels_last)) if r1 else
+                        (lambda x: x))
 
     def step(x, y):
         opt.zero_grad()
@@ -257,11 +318,15 @@ def main():
             dev_step(args.warmup + extra_warmup)
             extra_warmup += 1
         barrier_sync(world)
+        if hasattr(ddp, "reset_exposed_comm"):
+            ddp.reset_exposed_comm()     # exposed communication is reported for the timed (graph-replayed) steps only
         _lib.reset_launches()
         t_begin = time.monotonic()
         ms_total = timed_region(dev_step, args.steps, world)
         t_end = time.monotonic()
         launches = _lib.launches()
+        exposed = ddp.exposed_comm_ms(last=args.steps) if (args.impl == "ours" and hasattr(ddp, "exposed_comm_ms")) \
+            else None
         if len(clocks.rows) < 2:                    # very short runs: keep the load on until two samples exist
             t_wait = time.monotonic()
             while len(clocks.rows) < 2 and time.monotonic() - t_wait < 3.0:
@@ -302,9 +367,19 @@ def main():
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                "final_loss": float(loss_host[args.steps - 1])}
 
-    exposed = None
-    if args.impl == "ours" and hasattr(ddp, "exposed_comm_ms"):
-        exposed = ddp.exposed_comm_ms()
+    # ---- self-check: replicas bit-identical after all the timed steps (vouches for the collectives), loss finite
+    replicas_identical = None
+    if args.impl == "ours":
+        sums = gather_objects(replica_checksum(ddp), world)
+        replicas_identical = all(c == sums[0] for c in sums)
+    # ---- communication overhead of backward, same probe on both arms (runs last: it desynchronises nothing that
+    #      is measured afterwards)
+    overhead = None
+    if world > 1 and not args.no_comm_probe:
+        overhead = backward_comm_overhead(ddp, ddp._bench_parts, xs[0], ys[0], world,
+                                          autocast=(args.impl == "reference" and args.ref_variant == "r1"))
+        if args.impl == "reference":
+            exposed = overhead     # torch DDP offers no per-step tail timestamp; the differential is its figure
 
     if rank == 0:
         out = {
@@ -326,6 +401,11 @@ def main():
                        "cuda_graph": bool(getattr(getattr(ddp, "_bench_step", None), "captures", 0))},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "ours" else 0,
             "exposed_comm_ms_per_step": exposed,
+            "exposed_comm_how": ("device %globaltimer stamps inside the replayed graph: end of last reduction minus "
+                                 "end of backward compute" if args.impl == "ours" else
+                                 "backward(sync) - backward(no_sync), CUDA events"),
+            "comm_overhead_bwd_ms": overhead,
+            "replicas_identical": replicas_identical,
         }
         if args.impl == "reference":
             out["reference_variant"] = args.ref_variant

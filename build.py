@@ -21,9 +21,17 @@ LIB = os.path.join(LIBDIR, "libb200ddp.so")
 
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--use_fast_math", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
+# --use_fast_math (flush-to-zero, approximate division / rsqrt / exp / log) only where it is harmless: the tensor-core
+# conv / stem kernels, whose arithmetic is bf16 MMAs with fp32 accumulation. BatchNorm statistics and finalize, the
+# SGD / all-reduce epilogue and the cross-entropy keep IEEE fp32 semantics (denormal gradients and momentum survive).
+FAST_MATH_SOURCES = {"conv_igemm.cu", "stem.cu"}
+FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
          "-I" + os.path.join(ROOT, "include"), "-I" + CSRC, "--expt-relaxed-constexpr",
          "-diag-suppress", "177"] + os.environ.get("B200DDP_NVCC_FLAGS", "").split()
+
+
+def _flags_for(src):
+    return FLAGS + (["--use_fast_math"] if os.path.basename(src) in FAST_MATH_SOURCES else [])
 
 
 def _deps_hash(src):
@@ -33,7 +41,7 @@ def _deps_hash(src):
             if f.endswith((".h", ".cuh"))):
         with open(p, "rb") as fh:
             h.update(fh.read())
-    h.update(" ".join(ARCH + FLAGS).encode())
+    h.update(" ".join(ARCH + _flags_for(src)).encode())
     return h.hexdigest()
 
 
@@ -43,7 +51,7 @@ def _compile(src, force, verbose):
     want = _deps_hash(src)
     if not force and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == want:
         return obj, "", False
-    cmd = [NVCC] + ARCH + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+    cmd = [NVCC] + ARCH + _flags_for(src) + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
@@ -53,8 +61,20 @@ def _compile(src, force, verbose):
 
 
 def build(jobs=None, force=False, verbose=False, quiet=False):
+    """Compile and link under an inter-process lock: with `torchrun --nproc_per_node=8` on a fresh tree all ranks
+    reach the auto-build at once; the first one builds, the others wait and find everything up to date."""
     os.makedirs(OBJ, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
+    import fcntl
+    with open(os.path.join(ROOT, "build", ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return _build_locked(jobs, force, verbose, quiet)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(jobs, force, verbose, quiet):
     srcs = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
     jobs = jobs or min(len(srcs), os.cpu_count() or 4)
     objs, rebuilt = [], False
@@ -65,10 +85,12 @@ def build(jobs=None, force=False, verbose=False, quiet=False):
             if verbose and log:
                 print(log)
     if rebuilt or not os.path.exists(LIB):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lpthread", "-ldl", "-lrt"]
+        tmp = LIB + ".tmp.%d" % os.getpid()
+        cmd = [NVCC] + ARCH + ["-shared", "-o", tmp] + objs + ["-lpthread", "-ldl", "-lrt"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+        os.replace(tmp, LIB)      # never expose a half-written library to a process that is about to dlopen it
     if not quiet:
         print("built %s (%d sources, %s)" % (os.path.relpath(LIB, ROOT), len(srcs),
                                              "rebuilt" if rebuilt else "up to date"))

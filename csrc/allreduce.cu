@@ -26,7 +26,16 @@ struct SgdArgs {
   __nv_bfloat16* shadow;
   float lr, mu, wd;
   int first;
+  const float* hyper;         // optional device block {lr, momentum, weight_decay}: overrides the by-value copies
 };
+// Hyper-parameters come from device memory when a block is given, so a learning-rate schedule changes three
+// floats on the device instead of the arguments baked into a captured CUDA graph.
+B2_DEVICE SgdArgs load_hyper(SgdArgs a) {
+  if (a.p32 && a.hyper) {
+    a.lr = a.hyper[0]; a.mu = a.hyper[1]; a.wd = a.hyper[2];
+  }
+  return a;
+}
 
 B2_DEVICE float4 ld_peer_f4(const float* p) {
   uint4 u = ld_volatile_v4(p);
@@ -101,8 +110,11 @@ B2_DEVICE float4 reduce_peers(const XgpuCtx& xg, long long off_f, long long vi, 
 
 // ------------------------------------------------------------------------------------------------ one-shot
 __global__ void __launch_bounds__(kArThreads)
-    allreduce_oneshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd, int write_grad) {
+    allreduce_oneshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd_in, int write_grad) {
+  const SgdArgs sgd = load_hyper(sgd_in);
+  debug_skew(xg.rank, 0);
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 1);
   float4 keep[kOneShotMaxVecPerThread];
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -128,14 +140,17 @@ __global__ void __launch_bounds__(kArThreads)
 // ------------------------------------------------------------------------------------------------ two-shot
 template <int W>
 __global__ void __launch_bounds__(kArThreads)
-    allreduce_twoshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd, int write_grad) {
+    allreduce_twoshot_kernel(XgpuCtx xg, long long off_f, long long nvec, float scale, SgdArgs sgd_in, int write_grad) {
+  const SgdArgs sgd = load_hyper(sgd_in);
   constexpr int U = (W <= 4) ? 4 : 2;  // peer loads in flight per thread: W*U vectors
   const long long slice = (nvec + xg.world - 1) / xg.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   float* mine = xg.data[xg.rank] + off_f;
 
+  debug_skew(xg.rank, 0);
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 1);
   {  // reduce-scatter: this rank owns [s0, s1)
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
     for (long long vi = s0 + t0; vi < s1; vi += stride * U) {
@@ -147,6 +162,7 @@ __global__ void __launch_bounds__(kArThreads)
     }
   }
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 2);
   // all-gather (+ update): pull every owner's reduced slice; own slice is already local
   for (int q = 0; q < xg.world; ++q) {
     const int owner = (xg.rank + q) % xg.world;  // start with the local slice, then stagger peers
@@ -186,15 +202,23 @@ B2_DEVICE void multimem_st_f4(float* mc, float4 v) {
                "f"(v.z), "f"(v.w)
                : "memory");
 }
+// Every cross-GPU barrier pairs the SAME-NUMBERED CTA of each rank and nothing else, so after a barrier CTA b may
+// only consume what CTA b (of any rank) produced before it. All loops below therefore walk a slice as
+// s0(owner) + (b * blockDim + t) + k * stride: the vector set CTA b of the owner stored in phase 1 is exactly the
+// set CTA b of every rank loads in phase 2 (csrc/xgpu.cuh; B2_DEBUG_SKEW delays some CTAs to prove it, tests).
 __global__ void __launch_bounds__(kArThreads)
-    allreduce_multimem_kernel(XgpuCtx xg, float* mc_base, long long off_f, long long nvec, float scale, SgdArgs sgd) {
+    allreduce_multimem_kernel(XgpuCtx xg, float* mc_base, long long off_f, long long nvec, float scale, SgdArgs sgd_in) {
+  const SgdArgs sgd = load_hyper(sgd_in);
   const long long slice = (nvec + xg.world - 1) / xg.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   float* mc = mc_base + off_f;
   float* mine = xg.data[xg.rank] + off_f;
+  debug_skew(xg.rank, 0);
   xgpu_barrier(xg, blockIdx.x);
-  {
+  debug_skew(xg.rank, 1);
+  {  // own slice: switch-reduced load, scale, multicast store to every rank; the SGD update of this slice is
+     // applied straight from the registers (no second read)
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
     for (long long vi = s0 + t0; vi < s1; vi += stride * kUnroll) {
       float4 g[kUnroll];
@@ -206,24 +230,31 @@ __global__ void __launch_bounds__(kArThreads)
         if (vi + u * stride < s1) {
           g[u].x *= scale; g[u].y *= scale; g[u].z *= scale; g[u].w *= scale;
           multimem_st_f4(mc + (vi + u * stride) * 4, g[u]);  // lands in every rank's buffer
+          if (sgd.p32) sgd_apply4(sgd, vi + u * stride, g[u]);
         }
       }
     }
   }
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 2);
   if (sgd.p32) {
-    // local copy, filled by the multicast stores of every rank; read through L2 (never cached in this SM's L1)
-    for (long long vi = t0; vi < nvec; vi += stride * kUnroll) {
-      uint4 u[kUnroll];
+    // the other owners' slices of the local copy, filled by their multicast stores; read through L2 (never cached
+    // in this SM's L1), owner by owner in the order their same-numbered CTAs wrote them
+    for (int q = 1; q < xg.world; ++q) {
+      const int owner = (xg.rank + q) % xg.world;
+      const long long s0 = slice * owner, s1 = min(nvec, s0 + slice);
+      for (long long vi = s0 + t0; vi < s1; vi += stride * kUnroll) {
+        uint4 u[kUnroll];
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k)
-        if (vi + k * stride < nvec) u[k] = ld_cg_v4(mine + (vi + k * stride) * 4);
+        for (int k = 0; k < kUnroll; ++k)
+          if (vi + k * stride < s1) u[k] = ld_cg_v4(mine + (vi + k * stride) * 4);
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k)
-        if (vi + k * stride < nvec)
-          sgd_apply4(sgd, vi + k * stride,
-                     make_float4(__uint_as_float(u[k].x), __uint_as_float(u[k].y), __uint_as_float(u[k].z),
-                                 __uint_as_float(u[k].w)));
+        for (int k = 0; k < kUnroll; ++k)
+          if (vi + k * stride < s1)
+            sgd_apply4(sgd, vi + k * stride,
+                       make_float4(__uint_as_float(u[k].x), __uint_as_float(u[k].y), __uint_as_float(u[k].z),
+                                   __uint_as_float(u[k].w)));
+      }
     }
   }
 }
@@ -306,6 +337,20 @@ B2_DEVICE void cast_local_to_wire(const float* __restrict__ g32, __nv_bfloat16* 
                                    pack_bf16x2(b.z, b.w)));
   }
 }
+// Same cast, walked slice by slice (s0(owner) + t0 + k * stride): what CTA b of an owner reduces after the first
+// barrier is then exactly what CTA b of every rank cast before it.
+B2_DEVICE void cast_local_to_wire_sliced(const float* __restrict__ g32, __nv_bfloat16* wire, long long nvec8,
+                                         long long slice, int world, long long t0, long long stride) {
+  for (int q = 0; q < world; ++q) {
+    const long long s0 = slice * q, s1 = min(nvec8, s0 + slice);
+    for (long long v = s0 + t0; v < s1; v += stride) {
+      const float4 a = *reinterpret_cast<const float4*>(g32 + v * 8);
+      const float4 b = *reinterpret_cast<const float4*>(g32 + v * 8 + 4);
+      st_v4(wire + v * 8, make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y),
+                                     pack_bf16x2(b.z, b.w)));
+    }
+  }
+}
 template <int W>
 B2_DEVICE Bf16x8 reduce_wire(const XgpuCtx& xg, long long off_h, long long v8, float scale) {
   uint4 u[W];
@@ -331,11 +376,14 @@ B2_DEVICE Bf16x8 reduce_wire(const XgpuCtx& xg, long long off_h, long long v8, f
 template <int W>
 __global__ void __launch_bounds__(kArThreads)
     allreduce_oneshot_bf16_kernel(XgpuCtx xg, long long off_h, long long nvec8, float scale, const float* g32_in,
-                                  float* g32_out, SgdArgs sgd) {
+                                  float* g32_out, SgdArgs sgd_in) {
+  const SgdArgs sgd = load_hyper(sgd_in);
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  debug_skew(xg.rank, 0);
   cast_local_to_wire(g32_in, reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h, nvec8, t0, stride);
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 1);
   for (long long v = t0; v < nvec8; v += stride) consume_avg8(sgd, g32_out, v, reduce_wire<W>(xg, off_h, v, scale));
   xgpu_barrier(xg, blockIdx.x);  // peers are done with this rank's staging area
 }
@@ -343,18 +391,22 @@ __global__ void __launch_bounds__(kArThreads)
 template <int W>
 __global__ void __launch_bounds__(kArThreads)
     allreduce_twoshot_bf16_kernel(XgpuCtx xg, long long off_h, long long nvec8, float scale, const float* g32_in,
-                                  float* g32_out, SgdArgs sgd) {
+                                  float* g32_out, SgdArgs sgd_in) {
+  const SgdArgs sgd = load_hyper(sgd_in);
   const long long slice = (nvec8 + xg.world - 1) / xg.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   __nv_bfloat16* mine = reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h;
-  cast_local_to_wire(g32_in, mine, nvec8, t0, stride);
+  debug_skew(xg.rank, 0);
+  cast_local_to_wire_sliced(g32_in, mine, nvec8, slice, xg.world, t0, stride);
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 1);
   {
     const long long s0 = slice * xg.rank, s1 = min(nvec8, s0 + slice);
     for (long long v = s0 + t0; v < s1; v += stride) st_v4(mine + v * 8, pack_bf16x8(reduce_wire<W>(xg, off_h, v, scale)));
   }
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 2);
   for (int q = 0; q < xg.world; ++q) {
     const int owner = (xg.rank + q) % xg.world;
     const long long s0 = slice * owner, s1 = min(nvec8, s0 + slice);
@@ -385,25 +437,35 @@ B2_DEVICE void multimem_st_bf16x8(__nv_bfloat16* mc, uint4 v) {
 }
 __global__ void __launch_bounds__(kArThreads)
     allreduce_multimem_bf16_kernel(XgpuCtx xg, __nv_bfloat16* mc_base, long long off_h, long long nvec8, float scale,
-                                   const float* g32_in, float* g32_out, SgdArgs sgd) {
+                                   const float* g32_in, float* g32_out, SgdArgs sgd_in) {
+  const SgdArgs sgd = load_hyper(sgd_in);
   const long long slice = (nvec8 + xg.world - 1) / xg.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   __nv_bfloat16* mine = reinterpret_cast<__nv_bfloat16*>(xg.data[xg.rank]) + off_h;
   __nv_bfloat16* mc = mc_base + off_h;
-  cast_local_to_wire(g32_in, mine, nvec8, t0, stride);
+  debug_skew(xg.rank, 0);
+  cast_local_to_wire_sliced(g32_in, mine, nvec8, slice, xg.world, t0, stride);
   xgpu_barrier(xg, blockIdx.x);
+  debug_skew(xg.rank, 1);
   {
     const long long s0 = slice * xg.rank, s1 = min(nvec8, s0 + slice);
     for (long long v = s0 + t0; v < s1; v += stride) {
       Bf16x8 g = unpack_bf16x8(multimem_ld_reduce_bf16x8(mc + v * 8));
 #pragma unroll
       for (int j = 0; j < 8; ++j) g.v[j] *= scale;
-      multimem_st_bf16x8(mc + v * 8, pack_bf16x8(g));
+      const uint4 packed = pack_bf16x8(g);
+      multimem_st_bf16x8(mc + v * 8, packed);
+      consume_avg8(sgd, g32_out, v, unpack_bf16x8(packed));   // own slice: from the registers, rounded once
     }
   }
   xgpu_barrier(xg, blockIdx.x);
-  for (long long v = t0; v < nvec8; v += stride) consume_avg8(sgd, g32_out, v, unpack_bf16x8(ld_cg_v4(mine + v * 8)));
+  debug_skew(xg.rank, 2);
+  for (int q = 1; q < xg.world; ++q) {   // owner-relative: see allreduce_multimem_kernel
+    const int owner = (xg.rank + q) % xg.world;
+    const long long s0 = slice * owner, s1 = min(nvec8, s0 + slice);
+    for (long long v = s0 + t0; v < s1; v += stride) consume_avg8(sgd, g32_out, v, unpack_bf16x8(ld_cg_v4(mine + v * 8)));
+  }
 }
 
 // Plain device-side barrier (one CTA per rank): orders everything before it on all ranks' streams.
@@ -414,6 +476,7 @@ __global__ void barrier_kernel(XgpuCtx xg, int channel) { xgpu_barrier(xg, chann
 using namespace b2;
 
 B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_allreduce)
+B2_DEFINE_DEBUG_SKEW_SETTER(b2_set_debug_skew_ns_allreduce)
 
 static int clamp_blocks(int nblocks, long long nvec) {
   long long need = (nvec + kArThreads - 1) / kArThreads;
@@ -430,12 +493,13 @@ extern "C" long long b2_allreduce_oneshot_max_elems(int nblocks) {
 
 extern "C" int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long n, int algo,
                             float scale, float* p32, float* mom, void* shadow_bf16, float lr, float momentum,
-                            float weight_decay, int first_step, int write_grad, int nblocks, void* stream) {
+                            float weight_decay, int first_step, const float* hyper_dev, int write_grad, int nblocks,
+                            void* stream) {
   if (!ctx || n <= 0 || (n & 3) || (offset_bytes & 15)) return cudaErrorInvalidValue;
   XgpuCtx xg = xgpu_from_c(ctx);
   const long long nvec = n >> 2;
   const long long off_f = offset_bytes >> 2;
-  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step};
+  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step, hyper_dev};
   cudaStream_t st = (cudaStream_t)stream;
   if (algo == B2_AR_AUTO) {
     // One-shot moves (W-1)*S inbound per GPU but has two barriers and no second pass: wins only when small.
@@ -486,12 +550,12 @@ extern "C" int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long
 extern "C" int b2_allreduce_bf16(const b2_xgpu_ctx* ctx, void* mc_base, long long wire_offset_bytes, long long n,
                                  int algo, float scale, const float* g32_in, float* g32_out, float* p32, float* mom,
                                  void* shadow_bf16, float lr, float momentum, float weight_decay, int first_step,
-                                 int nblocks, void* stream) {
+                                 const float* hyper_dev, int nblocks, void* stream) {
   if (!ctx || n <= 0 || (n & 7) || (wire_offset_bytes & 15) || !g32_in) return cudaErrorInvalidValue;
   XgpuCtx xg = xgpu_from_c(ctx);
   const long long nvec8 = n >> 3;
   const long long off_h = wire_offset_bytes >> 1;
-  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step};
+  SgdArgs sgd{p32, mom, (__nv_bfloat16*)shadow_bf16, lr, momentum, weight_decay, first_step, hyper_dev};
   cudaStream_t st = (cudaStream_t)stream;
   if (algo == B2_AR_AUTO) {
     algo = (n * 2 <= (256 << 10)) ? B2_AR_ONESHOT : B2_AR_TWOSHOT;

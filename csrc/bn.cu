@@ -19,6 +19,8 @@ constexpr int kBnThreads = 256;
 #ifndef B2_BN_BLOCKS_PER_SM
 #define B2_BN_BLOCKS_PER_SM 4
 #endif
+// Capacity of the partial-sum scratch in rows (sized for a 148-SM B200; the launch grid is derived from the
+// device's actual SM count and clamped to this).
 constexpr int kMaxPartialBlocks = 148 * B2_BN_BLOCKS_PER_SM;
 
 struct Vec8 {
@@ -361,7 +363,9 @@ __global__ void __launch_bounds__(256)
 static int plan_blocks(long long M, int C, long long* rows_per_blk) {
   const int C8 = C / 8, RP = kBnThreads / C8;
   long long nblk = (M + (long long)RP * 8 - 1) / ((long long)RP * 8);
-  if (nblk > kMaxPartialBlocks) nblk = kMaxPartialBlocks;
+  long long cap = (long long)host_num_sms() * B2_BN_BLOCKS_PER_SM;
+  if (cap > kMaxPartialBlocks) cap = kMaxPartialBlocks;
+  if (nblk > cap) nblk = cap;
   if (nblk < 1) nblk = 1;
   long long rpb = (M + nblk - 1) / nblk;
   rpb = (rpb + RP - 1) / RP * RP;
@@ -372,7 +376,7 @@ static int plan_blocks(long long M, int C, long long* rows_per_blk) {
 
 static int stream_grid(long long nvec) {
   long long b = (nvec + 255) / 256;
-  const long long cap = 148LL * 16;
+  const long long cap = (long long)host_num_sms() * 16;
   return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
 }
 

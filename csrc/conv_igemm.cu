@@ -1429,16 +1429,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads3, 1)
   if (warp == 1) tmem_free_pair<2 * BN>(tmem_base);
 }
 
-static int g_num_sms = 0;
-static int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
-  }
-  return g_num_sms;
-}
+static int num_sms() { return b2::host_num_sms(); }
 
 template <int KIND, int AMODE, int BN, int MT = 1, int FAN = 0>
 static cudaError_t launch2(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p_in, int items,
@@ -1788,11 +1779,12 @@ extern "C" int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, in
   const int bn = flat ? 256 : bn_for(Cin, WGRAD, Cout);
   const long long tiles = flat ? (long long)((Cout + BM - 1) / BM) * ((taps * Cin + 255) / 256)
                                : (long long)((Cout + BM - 1) / BM) * (Cin / bn) * taps;
-  long long want = ((g_impl >= 2 ? 2 : 4) * 148 + tiles - 1) / tiles;
-  if (g_impl == 2 && g_wgrad_waves == 1 && tiles <= 148) want = 148 / tiles;   // one item per SM, single wave
+  const int sms = num_sms();
+  long long want = ((g_impl >= 2 ? 2 : 4) * sms + tiles - 1) / tiles;
+  if (g_impl == 2 && g_wgrad_waves == 1 && tiles <= sms) want = sms / tiles;   // one item per SM, single wave
   if (wgrad_mt2(bn, Cout)) {   // half as many (256-row) tiles, one item per SM in a single wave
     const long long t2 = tiles / 2;
-    want = 148 / t2;
+    want = sms / t2;
   }
   const long long wbytes = (long long)Cout * taps * Cin * 4;
   long long cap = ws_bytes / wbytes;

@@ -246,7 +246,10 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ m, float* o
 __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                   float* __restrict__ buf, __nv_bfloat16* __restrict__ shadow,
                                                   long long n, float lr, float mu, float wd, float gscale,
-                                                  int first) {
+                                                  int first, const float* __restrict__ hyper) {
+  if (hyper) {   // device-side hyper-parameters {lr, momentum, weight_decay}: a schedule never re-captures the graph
+    lr = hyper[0]; mu = hyper[1]; wd = hyper[2];
+  }
   const long long nv = n >> 2;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv;
        i += (long long)gridDim.x * blockDim.x) {
@@ -350,9 +353,19 @@ __global__ void nchw_to_nhwc_bf16_kernel(const T* __restrict__ x, __nv_bfloat16*
   }
 }
 
+// ------------------------------------------------------------------------------------------------ tracing / graph glue
+// ring[0] = number of stamps taken so far, ring[1 + i % cap] = %globaltimer (ns) of stamp i. One thread: the kernel
+// is a marker in stream order, so its time is "everything queued before it on this stream has finished".
+__global__ void timestamp_kernel(unsigned long long* ring, int cap) {
+  const unsigned long long i = ring[0];
+  ring[1 + (i % (unsigned long long)cap)] = global_timer_ns();
+  ring[0] = i + 1;
+}
+__global__ void set_ptr_slot_kernel(const void** slot, const void* value) { *slot = value; }
+
 static int sgrid(long long n, int per = 256) {
   long long b = (n + per - 1) / per;
-  const long long cap = 148LL * 16;
+  const long long cap = (long long)host_num_sms() * 16;
   return (int)(b < 1 ? 1 : (b < cap ? b : cap));
 }
 
@@ -416,10 +429,21 @@ extern "C" int b2_colsum_bf16(const void* m, float* out, int rows, int cols, int
   return cudaGetLastError();
 }
 extern "C" int b2_sgd_step(float* p, const float* g, float* buf, void* shadow_bf16, long long n, float lr,
-                           float momentum, float weight_decay, float grad_scale, int first_step, void* stream) {
+                           float momentum, float weight_decay, float grad_scale, int first_step,
+                           const float* hyper_dev, void* stream) {
   if (n <= 0) return 0;
   sgd_kernel<<<sgrid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(p, g, buf, (bf16*)shadow_bf16, n, lr, momentum,
-                                                                   weight_decay, grad_scale, first_step);
+                                                                   weight_decay, grad_scale, first_step, hyper_dev);
+  return cudaGetLastError();
+}
+extern "C" int b2_timestamp(unsigned long long* ring, int capacity, void* stream) {
+  if (!ring || capacity <= 0) return cudaErrorInvalidValue;
+  timestamp_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ring, capacity);
+  return cudaGetLastError();
+}
+extern "C" int b2_set_ptr_slot(void* slot, const void* value, void* stream) {
+  if (!slot) return cudaErrorInvalidValue;
+  set_ptr_slot_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((const void**)slot, value);
   return cudaGetLastError();
 }
 extern "C" int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {

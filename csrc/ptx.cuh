@@ -14,9 +14,24 @@ namespace b2 {
 // A spin that never ends hangs the GPU box (and costs a strike), so every wait in the library is
 // bounded in wall time: after B2_SPIN_TIMEOUT_NS the kernel traps and the launch surfaces as a CUDA error
 // on the host (the host-side watchdog in csrc/symm.cu then turns that into a clean non-zero exit).
+// The default is the process-group timeout of the reference stack (30 min, torch.distributed's default for
+// NCCL collectives): ranks legitimately wait for each other for minutes, e.g. while rank 0 alone evaluates and
+// writes the checkpoint (reference resnet/main.py:109-115). Tests and the benchmark set a short bound.
 #ifndef B2_SPIN_TIMEOUT_NS
-#define B2_SPIN_TIMEOUT_NS 20000000000ull  // 20 s (default; b2_set_spin_timeout_ms changes it at run time)
+#define B2_SPIN_TIMEOUT_NS 1800000000000ull  // 1800 s (default; b2_set_spin_timeout_ms changes it at run time)
 #endif
+
+// SM count of the current device (host side; grids and split factors are sized from it, never from a literal).
+static inline int host_num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;  // B200
+  }
+  return n;
+}
 
 B2_DEVICE uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 B2_DEVICE uint32_t lane_id() { return threadIdx.x & 31; }

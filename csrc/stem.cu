@@ -31,9 +31,13 @@ constexpr int kStemStages = 3;
 
 // ---------------------------------------------------------------------------------------------- packing
 // NCHW (fp32 or bf16) -> padded NHWC4 bf16 image, padding included (every element of xp is written).
+// x_slot (optional): device memory holding the address of the batch; the kernel then reads the batch through it, so
+// a captured CUDA graph can be pointed at a different input buffer before every replay (no copy into a static
+// buffer; utils/graph.py).
 template <typename T>
-__global__ void stem_pack_input_kernel(const T* __restrict__ x, uint2* __restrict__ xp, int N, int H, int W, int Hp,
-                                       int Wp) {
+__global__ void stem_pack_input_kernel(const T* __restrict__ x, const void* const* __restrict__ x_slot,
+                                       uint2* __restrict__ xp, int N, int H, int W, int Hp, int Wp) {
+  if (x_slot) x = reinterpret_cast<const T*>(*x_slot);
   const long long total = (long long)N * Hp * Wp;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -387,16 +391,7 @@ __global__ void __launch_bounds__(kStemWThreads, 1)
   if (warp == 1) tmem_free<128>(tmem_base);
 }
 
-static int stem_num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+static int stem_num_sms() { return b2::host_num_sms(); }
 
 struct StemGeom {
   int Ho, Wo, Hp, Wp;
@@ -439,18 +434,28 @@ extern "C" long long b2_stem_padded_elems(int N, int H, int W) {
   return (long long)N * g.Hp * g.Wp * 4;
 }
 
-extern "C" int b2_stem_pack_input(const void* x_nchw, int x_is_bf16, void* xp, int N, int H, int W, void* stream) {
+static int stem_pack_input_launch(const void* x_nchw, const void* const* x_slot, int x_is_bf16, void* xp, int N,
+                                  int H, int W, void* stream) {
   const StemGeom g = stem_geom(H, W);
   const long long total = (long long)N * g.Hp * g.Wp;
   long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  const long long cap = (long long)stem_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
   if (x_is_bf16)
     stem_pack_input_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)x_nchw, (uint2*)xp, N, H, W, g.Hp, g.Wp);
+        (const __nv_bfloat16*)x_nchw, x_slot, (uint2*)xp, N, H, W, g.Hp, g.Wp);
   else
-    stem_pack_input_kernel<float><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const float*)x_nchw, (uint2*)xp, N,
-                                                                                  H, W, g.Hp, g.Wp);
+    stem_pack_input_kernel<float><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const float*)x_nchw, x_slot,
+                                                                                  (uint2*)xp, N, H, W, g.Hp, g.Wp);
   return cudaGetLastError();
+}
+extern "C" int b2_stem_pack_input(const void* x_nchw, int x_is_bf16, void* xp, int N, int H, int W, void* stream) {
+  return stem_pack_input_launch(x_nchw, nullptr, x_is_bf16, xp, N, H, W, stream);
+}
+extern "C" int b2_stem_pack_input_indirect(const void* const* x_slot, int x_is_bf16, void* xp, int N, int H, int W,
+                                           void* stream) {
+  if (!x_slot) return cudaErrorInvalidValue;
+  return stem_pack_input_launch(nullptr, x_slot, x_is_bf16, xp, N, H, W, stream);
 }
 
 extern "C" int b2_stem_pack_weight(const float* w_ohwi, void* wp, void* stream) {

@@ -66,6 +66,7 @@ struct Drv {
   CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t,
                                unsigned long long);
   CUresult (*MulticastGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
   CUresult (*DeviceGetAttribute)(int*, CUdevice_attribute, CUdevice);
   bool ok = false;
 };
@@ -100,6 +101,7 @@ Drv& drv() {
     ok &= load(d.MulticastBindMem, "cuMulticastBindMem");
     ok &= load(d.MulticastGetGranularity, "cuMulticastGetGranularity");
     ok &= load(d.DeviceGetAttribute, "cuDeviceGetAttribute");
+    load(d.MulticastUnbind, "cuMulticastUnbind");   // optional: only needed by the teardown
     d.ok = ok;
   });
   return d;
@@ -219,6 +221,46 @@ extern "C" int b2_mc_bind_and_map(unsigned long long mc_handle, unsigned long lo
                                   (CUmemGenericAllocationHandle)mem_handle, 0, (size_t)bytes, 0);
   if (r != CUDA_SUCCESS) return r;
   return map_handle((CUmemGenericAllocationHandle)mc_handle, (size_t)bytes, device, mc_ptr);
+}
+
+// ---- teardown (everything the set-up calls above created, in reverse order) ------------------------------------
+// Unmap a mapping made by b2_vmm_alloc / b2_vmm_import / b2_mc_bind_and_map and give its address range back.
+extern "C" int b2_vmm_unmap(void* dptr, long long bytes) {
+  Drv& d = drv();
+  if (!d.ok) return cudaErrorNotSupported;
+  if (!dptr) return 0;
+  CUresult r = d.MemUnmap((CUdeviceptr)(uintptr_t)dptr, (size_t)bytes);
+  if (r != CUDA_SUCCESS) return r;
+  return d.MemAddressFree((CUdeviceptr)(uintptr_t)dptr, (size_t)bytes);
+}
+// Drop a generic allocation handle (the local window's, or a multicast object's). The physical memory / the
+// multicast object goes away when the last mapping and the last handle (on any rank) are gone.
+extern "C" int b2_vmm_release(unsigned long long handle) {
+  Drv& d = drv();
+  if (!d.ok) return cudaErrorNotSupported;
+  return d.MemRelease((CUmemGenericAllocationHandle)handle);
+}
+// Imported peer windows: b2_vmm_import maps and forgets the handle; this variant also returns it so that the
+// teardown can release it (an imported handle holds a reference on the peer's physical memory).
+extern "C" int b2_vmm_import_h(int fd, long long bytes, int device, void** dptr, unsigned long long* handle) {
+  Drv& d = drv();
+  if (!d.ok) return cudaErrorNotSupported;
+  CUmemGenericAllocationHandle h;
+  CUresult r = d.MemImportFromShareableHandle(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  if (r != CUDA_SUCCESS) return r;
+  int e = map_handle(h, (size_t)bytes, device, dptr);
+  if (e) {
+    d.MemRelease(h);
+    return e;
+  }
+  *handle = (unsigned long long)h;
+  return 0;
+}
+// Unbind this device's window from the multicast object (before unmapping / releasing either).
+extern "C" int b2_mc_unbind(unsigned long long mc_handle, int device, long long bytes) {
+  Drv& d = drv();
+  if (!d.ok || !d.MulticastUnbind) return cudaErrorNotSupported;
+  return d.MulticastUnbind((CUmemGenericAllocationHandle)mc_handle, device, 0, (size_t)bytes);
 }
 
 // ------------------------------------------------------------------------------------------------ fd passing

@@ -37,6 +37,24 @@ B2_DEVICE float ld_relaxed_sys_f32(const float* p) {
   return v;
 }
 
+// Debug aid for the signal protocols (SURVEY 5.2 "poisoned buffer / skew" mode): with a non-zero skew a
+// pseudo-random subset of the CTAs (different per rank and per phase) sleeps for that long at the marked points of
+// the collective kernels, so CTAs of one rank are far apart in progress. A kernel that consumes data which a
+// DIFFERENTLY numbered CTA of a peer produced - the barrier below does not order that - then reads stale values
+// and the numerical tests fail instead of passing by lock-step luck (tests/test_multigpu.py).
+static __device__ unsigned long long g_debug_skew_ns = 0;
+#define B2_DEFINE_DEBUG_SKEW_SETTER(name)                                                          \
+  extern "C" int name(unsigned long long ns) {                                                     \
+    return (int)cudaMemcpyToSymbol(b2::g_debug_skew_ns, &ns, sizeof(ns), 0, cudaMemcpyHostToDevice); \
+  }
+B2_DEVICE void debug_skew(int rank, int phase) {
+  const unsigned long long ns = g_debug_skew_ns;
+  if (ns == 0) return;
+  if (((blockIdx.x * 7u + (unsigned)rank * 3u + (unsigned)phase * 5u) & 3u) != 1u) return;
+  const uint64_t t0 = global_timer_ns();
+  while (global_timer_ns() - t0 < ns) __nanosleep(20000);
+}
+
 // Barrier across the same-numbered CTA of every rank. Must be reached by all threads of the CTA.
 // Pad layout on rank r: flags[r][channel * B2_MAX_WORLD + src] = last epoch signalled by rank `src`.
 // Everything this CTA wrote before the call is visible to every peer CTA after it returns.

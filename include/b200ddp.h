@@ -153,10 +153,22 @@ int b2_ce_fwd(const void* logits, const long long* labels, float* lse, float* lo
 int b2_ce_bwd(const void* logits, const long long* labels, const float* lse, const float* gscale, void* dlogits,
               float* dbias, int accumulate_bias, int rows, int ncls, int ld, void* stream);
 int b2_colsum_bf16(const void* m, float* out, int rows, int cols, int ld, int accumulate, void* stream);
-/* p, g, buf: flat fp32; shadow: optional bf16 copy of p refreshed in the same pass. */
+/* p, g, buf: flat fp32; shadow: optional bf16 copy of p refreshed in the same pass.
+ * hyper_dev (nullable): three floats in device memory {lr, momentum, weight_decay} read by the kernel instead of the
+ * by-value arguments, so a learning-rate schedule does not change the launch (and a captured CUDA graph stays valid). */
 int b2_sgd_step(float* p, const float* g, float* buf, void* shadow_bf16, long long n, float lr, float momentum,
-                float weight_decay, float grad_scale, int first_step, void* stream);
+                float weight_decay, float grad_scale, int first_step, const float* hyper_dev, void* stream);
 int b2_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+/* Tracing inside CUDA-graph replays (per-bucket ready / launch / done timestamps, exposed communication):
+ * a one-thread marker kernel that appends the GPU's %globaltimer (ns) to a device ring. ring[0] counts the stamps,
+ * ring[1 + i % capacity] holds stamp i; the ring must hold capacity + 1 u64 and start zeroed. Stamps on different
+ * streams of one GPU share a clock, so "comm stream done" minus "compute stream done" is the exposed communication
+ * of a step whether the step was launched from Python or replayed from a graph. No reference counterpart (the
+ * reference has no timers; torch's Reducer samples similar times every 100 iterations). */
+int b2_timestamp(unsigned long long* ring, int capacity, void* stream);
+/* *slot = value, in stream order (a one-thread kernel, so it can sit between graph replays): lets a captured graph
+ * read its input batch through a pointer that is re-aimed before every replay (b2_stem_pack_input_indirect). */
+int b2_set_ptr_slot(void* slot, const void* value, void* stream);
 int b2_stem_im2col(const void* x_nchw, int x_is_bf16, void* A, int N, int H, int W, void* stream);
 /* Direct stem (csrc/stem.cu): the 7x7/2 convolution on the tensor cores straight from a zero-padded NHWC4 bf16 copy
  * of the batch (overlapping-window TMA boxes), no im2col matrix in memory. b2_stem_supported: output width <= 112.
@@ -166,6 +178,9 @@ int b2_stem_im2col(const void* x_nchw, int x_is_bf16, void* A, int N, int H, int
 int b2_stem_supported(int H, int W);
 long long b2_stem_padded_elems(int N, int H, int W);
 int b2_stem_pack_input(const void* x_nchw, int x_is_bf16, void* xp, int N, int H, int W, void* stream);
+/* Same as b2_stem_pack_input, but the batch address is read from device memory (*x_slot) when the kernel runs. */
+int b2_stem_pack_input_indirect(const void* const* x_slot, int x_is_bf16, void* xp, int N, int H, int W,
+                                void* stream);
 int b2_stem_pack_weight(const float* w_ohwi, void* wp, void* stream);
 int b2_stem_fprop(const void* xp, const void* wp, void* y, int N, int H, int W, float* stats, int* stats_blocks,
                   void* stream);
@@ -209,6 +224,14 @@ int b2_mc_import(int fd, unsigned long long* mc_handle);
 int b2_mc_add_device(unsigned long long mc_handle, int device);
 int b2_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_handle, long long bytes, int device,
                        void** mc_ptr);
+/* Teardown (destroy_process_group / SymmetricWindow.close()): unbind from the multicast object, unmap every mapping
+ * (own window, peers' windows, multicast address) and free its address range, release every handle. After the last
+ * rank has done so the physical memory and the multicast object are gone. b2_vmm_import_h is b2_vmm_import that also
+ * returns the imported handle so that it can be released. */
+int b2_vmm_import_h(int fd, long long bytes, int device, void** dptr, unsigned long long* handle);
+int b2_vmm_unmap(void* dptr, long long bytes);
+int b2_vmm_release(unsigned long long handle);
+int b2_mc_unbind(unsigned long long mc_handle, int device, long long bytes);
 int b2_fd_listen(const char* name);
 int b2_fd_serve(int listen_sock, const int* fds, int nfds, int count);
 int b2_fd_fetch(const char* name, int which, int timeout_ms);
@@ -228,7 +251,8 @@ enum { B2_AR_AUTO = 0, B2_AR_ONESHOT = 1, B2_AR_TWOSHOT = 2, B2_AR_MULTIMEM = 3 
 long long b2_allreduce_oneshot_max_elems(int nblocks);
 int b2_allreduce(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long n, int algo, float scale,
                  float* p32, float* mom, void* shadow_bf16, float lr, float momentum, float weight_decay,
-                 int first_step, int write_grad, int nblocks, void* stream);
+                 int first_step, const float* hyper_dev /* nullable, see b2_sgd_step */, int write_grad, int nblocks,
+                 void* stream);
 int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbytes, int src, void* dst_override,
                  int nblocks, void* stream);
 /* bf16 wire format (the counterpart of torch's bf16_compress_hook): the kernel casts this rank's fp32 bucket
@@ -236,15 +260,21 @@ int b2_broadcast(const b2_xgpu_ctx* ctx, long long offset_bytes, long long nbyte
  * fp32, rounds the average to bf16 once, and feeds the SGD epilogue / g32_out (optional) from that value. */
 int b2_allreduce_bf16(const b2_xgpu_ctx* ctx, void* mc_base, long long wire_offset_bytes, long long n, int algo,
                       float scale, const float* g32_in, float* g32_out, float* p32, float* mom, void* shadow_bf16,
-                      float lr, float momentum, float weight_decay, int first_step, int nblocks, void* stream);
+                      float lr, float momentum, float weight_decay, int first_step, const float* hyper_dev,
+                      int nblocks, void* stream);
 /* Broadcast through the NVSwitch multicast mapping: only the source rank stores, the switch replicates. */
 int b2_broadcast_mc(const b2_xgpu_ctx* ctx, void* mc_base, long long offset_bytes, long long nbytes, int src,
                     int nblocks, void* stream);
 int b2_xgpu_barrier(const b2_xgpu_ctx* ctx, int channel, void* stream);
-/* Device-side waits on peers trap after this long (default 20 s). One setter per translation unit that spins;
- * parallel/comm.py calls both. */
+/* Device-side waits on peers trap after this long (default 1800 s, the reference stack's process-group timeout:
+ * ranks legitimately wait minutes for rank 0's evaluation + checkpoint, resnet/main.py:109-115). One setter per
+ * translation unit that spins; parallel/comm.py calls both. */
 int b2_set_spin_timeout_ns_allreduce(unsigned long long ns);
 int b2_set_spin_timeout_ns_bn(unsigned long long ns);
+/* Protocol debugging: a non-zero value makes a pseudo-random subset of the CTAs of every collective
+ * kernel sleep that long before and between the phases, so that a kernel which consumes data produced by a
+ * differently-numbered CTA of a peer (not ordered by the per-CTA cross-GPU barrier) fails its numerical test. */
+int b2_set_debug_skew_ns_allreduce(unsigned long long ns);
 
 #ifdef __cplusplus
 }

@@ -107,6 +107,9 @@ class ResNet(nn.Module):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
         self._engine = None
+        # device int64[1] holding the address of the input batch, or None: when set (utils/graph.py), the stem reads
+        # the batch through it, so a captured step can be pointed at a fresh input buffer before every replay
+        self._b2_input_slot = None
 
     def _make_layer(self, block, planes, blocks, stride=1):
         downsample = None
@@ -125,8 +128,22 @@ class ResNet(nn.Module):
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         return self.fc(torch.flatten(self.avgpool(x), 1))
 
+    def _engine_applies(self):
+        """The engine implements training-mode BatchNorm backward only. A forward that will be differentiated while
+        (some) BatchNorm layers normalise with their running statistics - ``model.eval()`` with grad enabled
+        (saliency maps, input gradients) or frozen-BN fine-tuning where single layers are in eval mode - goes through
+        the stock autograd path instead, which differentiates those layers correctly."""
+        if not torch.is_grad_enabled():
+            return True
+        bns = getattr(self, "_bn_modules", None)
+        if bns is None:
+            bns = self._bn_modules = [m for m in self.modules() if isinstance(m, nn.modules.batchnorm._BatchNorm)]
+        if not self.training:
+            return not any(p.requires_grad for p in self.parameters())
+        return all(m.training for m in bns)
+
     def forward(self, x):
-        if _lib.use_native(x) and next(self.parameters()).is_cuda:
+        if _lib.use_native(x) and next(self.parameters()).is_cuda and self._engine_applies():
             if self._engine is None:
                 self._engine = ResNetEngine(self)
                 self._engine.xg = getattr(self, "_b2_xgpu_ctx", None)
@@ -307,7 +324,9 @@ class ResNetEngine:
         blocks = 0
         if self.stem_direct and native.stem_supported(h, w):
             # tensor-core convolution straight from a padded NHWC4 copy of the batch (csrc/stem.cu)
-            xp = native.stem_pack_input(xin)
+            xp = native.stem_pack_input(xin, slot=m._b2_input_slot)
+            if m._b2_input_slot is not None:
+                m._b2_input_slot_used = True
             native.stem_pack_weight(w_ohwi, self.stem_wp_direct)
             y, blocks = native.stem_fprop(xp, self.stem_wp_direct, n, h, w,
                                           native.bn_partial(self.device) if want_stats else None)

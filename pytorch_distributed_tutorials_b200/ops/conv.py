@@ -185,13 +185,29 @@ def conv_wgrad(x, dy, w_shape, stride, pad, out=None, accumulate=False):
 
 
 # ------------------------------------------------------------------------------------------ torch oracle
+class _true_fp32:
+    """cuDNN convolutions of fp32 tensors run as TF32 by default (10-bit mantissa - about what bf16 inputs carry);
+    an oracle has to be real fp32, so TF32 is switched off around every reference call."""
+
+    def __enter__(self):
+        self.old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+
+    def __exit__(self, *exc):
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = self.old
+
+
 def ref_fprop(x, w, stride, pad):
-    return F.conv2d(x, w, None, stride, pad)
+    with _true_fp32():
+        return F.conv2d(x, w, None, stride, pad)
 
 
 def ref_dgrad(dy, w, x_shape, stride, pad):
-    return torch.nn.grad.conv2d_input(x_shape, w, dy, stride, pad)
+    with _true_fp32():
+        return torch.nn.grad.conv2d_input(x_shape, w, dy, stride, pad)
 
 
 def ref_wgrad(x, dy, w_shape, stride, pad):
-    return torch.nn.grad.conv2d_weight(x, w_shape, dy, stride, pad)
+    with _true_fp32():
+        return torch.nn.grad.conv2d_weight(x, w_shape, dy, stride, pad)

@@ -183,11 +183,19 @@ def colsum_bf16(m, out, accumulate=False):
 
 
 # ------------------------------------------------------------------------------------------------ optimizer
-def sgd_step(p, g, buf, shadow, lr, momentum, weight_decay, grad_scale, first_step):
-    """torch.optim.SGD (momentum, weight decay, dampening 0) on flat fp32 buffers + bf16 shadow refresh."""
+def sgd_step(p, g, buf, shadow, lr, momentum, weight_decay, grad_scale, first_step, hyper=None):
+    """torch.optim.SGD (momentum, weight decay, dampening 0) on flat fp32 buffers + bf16 shadow refresh.
+    ``hyper``: optional device tensor {lr, momentum, weight_decay} the kernel reads instead of the scalars."""
     n = p.numel()
     check(_lib.lib().b2_sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), c_ll(n), c_f(lr), c_f(momentum),
-                                 c_f(weight_decay), c_f(grad_scale), int(first_step), stream_ptr()), "b2_sgd_step")
+                                 c_f(weight_decay), c_f(grad_scale), int(first_step), ptr(hyper), stream_ptr()),
+          "b2_sgd_step")
+    count_launch()
+
+
+def set_ptr_slot(slot, tensor):
+    """``slot[0] = tensor.data_ptr()`` in stream order (one-thread kernel; usable between CUDA-graph replays)."""
+    check(_lib.lib().b2_set_ptr_slot(ptr(slot), ptr(tensor), stream_ptr()), "b2_set_ptr_slot")
     count_launch()
 
 
@@ -225,16 +233,22 @@ def stem_supported(h, w):
     return bool(_lib.lib().b2_stem_supported(int(h), int(w)))
 
 
-def stem_pack_input(x):
+def stem_pack_input(x, slot=None):
     """[N,3,H,W] fp32/bf16 NCHW -> zero-padded NHWC4 bf16 image (flat) for the direct stem kernels
-    (the 7x7/2 conv1 of the torchvision ResNet the reference builds at resnet/main.py:76)."""
+    (the 7x7/2 conv1 of the torchvision ResNet the reference builds at resnet/main.py:76).
+    ``slot`` (device int64[1], optional): the kernel reads the batch from the address stored there instead of from
+    ``x`` (which then only supplies shape and dtype); see ``set_ptr_slot``."""
     n, c, h, w = x.shape
     assert c == 3 and x.is_contiguous()
     lib = _lib.lib()
     lib.b2_stem_padded_elems.restype = ctypes.c_longlong
     xp = torch.empty(lib.b2_stem_padded_elems(n, h, w), dtype=torch.bfloat16, device=x.device)
-    check(lib.b2_stem_pack_input(ptr(x), int(x.dtype == torch.bfloat16), ptr(xp), n, h, w, stream_ptr()),
-          "b2_stem_pack_input")
+    if slot is not None:
+        check(lib.b2_stem_pack_input_indirect(ptr(slot), int(x.dtype == torch.bfloat16), ptr(xp), n, h, w,
+                                              stream_ptr()), "b2_stem_pack_input_indirect")
+    else:
+        check(lib.b2_stem_pack_input(ptr(x), int(x.dtype == torch.bfloat16), ptr(xp), n, h, w, stream_ptr()),
+              "b2_stem_pack_input")
     count_launch()
     return xp
 

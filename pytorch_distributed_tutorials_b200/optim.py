@@ -33,6 +33,7 @@ class SGD(torch.optim.SGD):
             for st in self._stores:
                 st.optimizer = self
         self._fused_done = set()  # bucket ids already updated by the reduce kernel in this iteration
+        self._hyper_dev = {}      # device -> (tensor {lr, momentum, weight_decay}, values it holds)
 
     # ------------------------------------------------------------------ fused path plumbing
     def _native_ok(self):
@@ -50,6 +51,22 @@ class SGD(torch.optim.SGD):
         g = self.param_groups[0]
         return float(g["lr"]), float(g["momentum"]), float(g["weight_decay"])
 
+    def hyper_dev(self, device):
+        """Device-side copy of (lr, momentum, weight_decay). The native kernels read their hyper-parameters from
+        this block, so a learning-rate schedule (``param_groups[0]["lr"] = ...``, any torch scheduler) changes
+        three floats on the device and a captured CUDA graph of the step stays valid (utils/graph.py)."""
+        vals = self.hyper()
+        ent = self._hyper_dev.get(device)
+        if ent is None:
+            ent = [torch.tensor(vals, dtype=torch.float32, device=device), vals]
+            self._hyper_dev[device] = ent
+        elif ent[1] != vals:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("optimizer hyper-parameters changed inside a CUDA graph capture")
+            ent[0].copy_(torch.tensor(vals, dtype=torch.float32))
+            ent[1] = vals
+        return ent[0]
+
     def has_momentum_state(self, st):
         """True once momentum buffers exist for this store's parameters (after the first step or a loaded
         state_dict); the kernels then compute ``mu*buf + g`` instead of initialising ``buf = g``."""
@@ -59,13 +76,13 @@ class SGD(torch.optim.SGD):
 
     def prepare_fused(self, st):
         """Called by the DDP reducer before it launches fused reduce+update kernels for this iteration.
-        Returns (lr, momentum, weight_decay, first_step)."""
+        Returns (lr, momentum, weight_decay, first_step, device hyper-parameter block)."""
         st.ensure_momentum()
         has = self.has_momentum_state(st)
         if has:
             self._bind_state(st)
         lr, mu, wd = self.hyper()
-        return lr, mu, wd, (not has)
+        return lr, mu, wd, (not has), self.hyper_dev(st.device)
 
     def _bind_state(self, st):
         """Expose the flat momentum buffer through torch's per-parameter state (state_dict parity)."""
@@ -104,13 +121,14 @@ class SGD(torch.optim.SGD):
             if has:
                 self._bind_state(st)  # adopt buffers that came from load_state_dict
             first = not has
+            hyper = self.hyper_dev(st.device)
             for b in st.buckets:
                 if id(b) in self._fused_done:
                     continue  # already applied by the all-reduce epilogue during backward
                 if any(p.grad is None for p in b.params):
                     self._step_bucket_sparse(st, b, lr, mu, wd, first)
                     continue
-                native.sgd_step(b.p32, b.g32, b.mom, b.shadow, lr, mu, wd, 1.0, first)
+                native.sgd_step(b.p32, b.g32, b.mom, b.shadow, lr, mu, wd, 1.0, first, hyper)
             st.mark_params_updated_natively()
             self._bind_state(st)
         self._fused_done.clear()
@@ -119,9 +137,10 @@ class SGD(torch.optim.SGD):
 
     def _step_bucket_sparse(self, st, b, lr, mu, wd, first):
         # Some parameter of the bucket got no gradient: update the others one by one (torch skips grad=None).
+        hyper = self.hyper_dev(st.device)
         for p, off in zip(b.params, b.offsets):
             if p.grad is None:
                 continue
             n = p.numel()
             native.sgd_step(b.p32[off:off + n], b.g32[off:off + n], b.mom[off:off + n], b.shadow[off:off + n], lr,
-                            mu, wd, 1.0, first)
+                            mu, wd, 1.0, first, hyper)

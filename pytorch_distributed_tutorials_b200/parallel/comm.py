@@ -45,8 +45,8 @@ class LocalComm(_Base):
         self.launch_log.append(("allreduce", bucket.index))
         if sgd is not None:
             from ..ops import native
-            lr, mu, wd, first = sgd
-            native.sgd_step(bucket.p32, bucket.g32, bucket.mom, bucket.shadow, lr, mu, wd, 1.0, first)
+            lr, mu, wd, first, hyper = (tuple(sgd) + (None,))[:5]
+            native.sgd_step(bucket.p32, bucket.g32, bucket.mom, bucket.shadow, lr, mu, wd, 1.0, first, hyper)
 
     def broadcast_(self, tensors, src=0):
         self.launch_log.append(("broadcast", len(tensors)))
@@ -115,8 +115,15 @@ class P2PComm(_Base):
         if t:
             self.set_spin_timeout_ms(int(t))
 
+    def set_debug_skew_us(self, us):
+        """Protocol debugging: delay a pseudo-random subset of the CTAs of every collective kernel by ``us``
+        microseconds before / between the phases (0 = off). See csrc/xgpu.cuh ``debug_skew``."""
+        check(_lib.lib().b2_set_debug_skew_ns_allreduce(ctypes.c_ulonglong(int(us) * 1000)),
+              "b2_set_debug_skew_ns_allreduce")
+
     def set_spin_timeout_ms(self, ms):
-        """How long a kernel may wait for a peer before it traps (failure detection; default 20 s)."""
+        """How long a kernel may wait for a peer before it traps (failure detection; default 1800 s, the
+        process-group timeout of the reference stack)."""
         ns = ctypes.c_ulonglong(int(ms) * 1000000)
         check(_lib.lib().b2_set_spin_timeout_ns_allreduce(ns), "b2_set_spin_timeout_ns_allreduce")
         check(_lib.lib().b2_set_spin_timeout_ns_bn(ns), "b2_set_spin_timeout_ns_bn")
@@ -154,27 +161,28 @@ class P2PComm(_Base):
         if self.wire == "bf16":
             return self._allreduce_bucket_bf16(bucket, sgd, a, st)
         off = self.window.offset_of(bucket.g32)
-        if sgd is not None:
-            lr, mu, wd, first = sgd
-            args = (ptr(bucket.p32), ptr(bucket.mom), ptr(bucket.shadow), c_f(lr), c_f(mu), c_f(wd), int(first))
-        else:
-            args = (c_p(0), c_p(0), c_p(0), c_f(0.0), c_f(0.0), c_f(0.0), 0)
+        args = self._sgd_args(bucket, sgd)
         e = _lib.lib().b2_allreduce(ctypes.byref(self.window.ctx(self.PAD_COMM)), c_p(self.mc_base or 0), c_ll(off),
                                     c_ll(bucket.numel), a, c_f(1.0 / self.world), *args, int(self.write_grad),
                                     self.nblocks, c_p(st.cuda_stream))
         check(e, "b2_allreduce")
         _lib.count_launch()
 
+    @staticmethod
+    def _sgd_args(bucket, sgd):
+        """(p32, momentum, bf16 shadow, lr, mu, wd, first step, device hyper-parameter block) of the fused update."""
+        if sgd is None:
+            return (c_p(0), c_p(0), c_p(0), c_f(0.0), c_f(0.0), c_f(0.0), 0, c_p(0))
+        lr, mu, wd, first, hyper = (tuple(sgd) + (None,))[:5]
+        return (ptr(bucket.p32), ptr(bucket.mom), ptr(bucket.shadow), c_f(lr), c_f(mu), c_f(wd), int(first),
+                ptr(hyper))
+
     def _allreduce_bucket_bf16(self, bucket, sgd, a, st):
         """bf16 wire: the kernel casts the fp32 bucket into a bf16 staging area of the window and reduces that."""
         wire = getattr(bucket, "wire16", None)
         if wire is None:
             wire = bucket.wire16 = self.alloc_tensor(bucket.numel, torch.bfloat16)
-        if sgd is not None:
-            lr, mu, wd, first = sgd
-            args = (ptr(bucket.p32), ptr(bucket.mom), ptr(bucket.shadow), c_f(lr), c_f(mu), c_f(wd), int(first))
-        else:
-            args = (c_p(0), c_p(0), c_p(0), c_f(0.0), c_f(0.0), c_f(0.0), 0)
+        args = self._sgd_args(bucket, sgd)
         g_out = ptr(bucket.g32) if (self.write_grad or sgd is None) else c_p(0)
         e = _lib.lib().b2_allreduce_bf16(ctypes.byref(self.window.ctx(self.PAD_COMM)), c_p(self.mc_base or 0),
                                          c_ll(self.window.offset_of(wire)), c_ll(bucket.numel), a,

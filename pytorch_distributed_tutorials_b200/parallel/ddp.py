@@ -30,6 +30,43 @@ from .comm import LocalComm, P2PComm, TorchComm
 from .flat import FlatParameterStore, plan_buckets
 
 MiB = 1 << 20
+_LIVE = weakref.WeakSet()   # wrappers whose symmetric windows destroy_process_group() must release
+
+
+def close_all():
+    """Release the peer-memory windows of every live wrapper (called by ``destroy_process_group``)."""
+    for d in list(_LIVE):
+        d.close()
+
+
+def split_tail_bucket(bucket_of_param, sizes_bytes, tail_bytes):
+    """Give the parameters whose gradients arrive LAST their own small bucket.
+
+    The last bucket of the plan (stem + first stage for a ResNet: 9.3 MiB for ResNet-50) is the only
+    one whose reduction has no backward compute left to hide behind. Cutting it so that only the final
+    ``tail_bytes`` of gradients wait for the very end of backward turns the exposed tail into one small,
+    latency-bound kernel; the rest of the old last bucket is reduced while the first stage's backward still runs.
+    Pure function of the plan (every rank computes the same split)."""
+    if tail_bytes <= 0 or not bucket_of_param:
+        return list(bucket_of_param)
+    last = bucket_of_param[-1]
+    idx = [i for i, b in enumerate(bucket_of_param) if b == last]
+    total = sum(sizes_bytes[i] for i in idx)
+    if len(idx) < 2 or total <= 2 * tail_bytes:
+        return list(bucket_of_param)
+    acc, cut = 0, None
+    for i in reversed(idx):
+        acc += sizes_bytes[i]
+        if acc > tail_bytes:
+            break
+        cut = i
+    if cut is None or cut == idx[0]:
+        return list(bucket_of_param)
+    out = list(bucket_of_param)
+    for i in idx:
+        if i >= cut:
+            out[i] = last + 1
+    return out
 
 
 def _ready_order(module, params):
@@ -45,7 +82,7 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
                  process_group=None, bucket_cap_mb=None, find_unused_parameters=False,
                  gradient_as_bucket_view=True, static_graph=False, backend=None, comm_algo=None,
-                 init_sync=True, gradient_wire=None):
+                 init_sync=True, gradient_wire=None, tail_bucket_mb=None):
         super().__init__()
         if find_unused_parameters:
             raise NotImplementedError("find_unused_parameters is not supported (ResNets use every parameter)")
@@ -75,6 +112,7 @@ class DistributedDataParallel(nn.Module):
         sizes = [p.numel() * p.element_size() for p in ordered]
         self.bucket_of_param = plan_buckets(sizes, first_cap, cap)
         self.bucket_cap_bytes = cap
+        self._tail_bucket_mb = tail_bucket_mb
 
         # ---- K1: every rank must hold the same parameter shapes
         if self.world > 1:
@@ -95,6 +133,12 @@ class DistributedDataParallel(nn.Module):
             else:
                 backend = "torch"
         buffers = [b for b in module.buffers()]
+        # exposed-tail cut (P2P backend only; the CPU / torch back ends keep torch's exact bucket tables)
+        tail = self._tail_bucket_mb
+        if tail is None:
+            tail = float(os.environ.get("B200DDP_TAIL_BUCKET_MB", "1" if backend == "p2p" else "0"))
+        if tail > 0 and self.world > 1:
+            self.bucket_of_param = split_tail_bucket(self.bucket_of_param, sizes, int(tail * MiB))
         if backend == "p2p":
             total = sum((p.numel() + 63) // 64 * 64 for p in ordered) * 4
             buf_bytes = sum((b.numel() * b.element_size() + 255) // 256 * 256 for b in buffers)
@@ -140,11 +184,25 @@ class DistributedDataParallel(nn.Module):
         self.debug = os.environ.get("B200DDP_DEBUG", "0") == "1"
         self._iter_log_start = 0
         self.measure_exposed = os.environ.get("B200DDP_MEASURE_EXPOSED", "1") == "1"
-        self._exposed_events = []
+        # device-side timestamps (csrc/misc.cu timestamp_kernel): [count, stamp ring] on the compute stream at the
+        # end of backward and on the communication stream after the last reduction. Marker kernels are part of a
+        # captured graph like any other launch, so exposed communication is measured in steady-state replays too.
+        self._ts_cap = 256
+        self._ts_compute = self._ts_comm = None
+        if self.measure_exposed and backend == "p2p":
+            self._ts_compute = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
+            self._ts_comm = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
+        self.trace_buckets = os.environ.get("B200DDP_TRACE", "0") == "1" and backend == "p2p"
+        self._bucket_rings = {}
+        self._buffers_in_sync = bool(init_sync) or self.world == 1   # constructor broadcast done; False after load_state_dict
+        self._post_forward_sync = backend == "p2p" and os.environ.get("B200DDP_BUFFER_SYNC", "post") == "post"
+        self._buffer_sync_pending = False
         self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook) for p in ordered]
         self.iterations = 0
         self.xgpu_compute_ctx = self.comm.window.ctx(P2PComm.PAD_COMPUTE) if backend == "p2p" else None
         self._install_syncbn_ctx()
+        _LIVE.add(self)
+        self._closed = False
         self._watchdog_evt = None
         wd = int(os.environ.get("B200DDP_WATCHDOG_SEC", "0"))
         if wd > 0 and self.device.type == "cuda":
@@ -177,13 +235,21 @@ class DistributedDataParallel(nn.Module):
         self._buffers_flat = region
         self._buffer_list = [b for b in self.module.buffers()]
 
-    def _sync_buffers(self):
-        """K3: broadcast BN buffers from rank 0 before a training forward."""
+    def _sync_buffers(self, stream=None):
+        """K3: broadcast BN buffers from rank 0 (before a training forward, or - P2P backend - right after it on the
+        communication stream, see forward())."""
         if self.world == 1 or not self._buffer_list:
             return
         if self._buffers_flat is not None:
             self.comm.launch_log.append(("broadcast", len(self._buffer_list)))
-            self.comm.broadcast_window_(self.comm.window.offset_of(self._buffers_flat), self._buffers_flat.numel(), 0)
+            pad = None
+            if stream is not None:
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+                stream.wait_event(ev)
+                pad = P2PComm.PAD_COMM
+            self.comm.broadcast_window_(self.comm.window.offset_of(self._buffers_flat), self._buffers_flat.numel(), 0,
+                                        stream=stream, pad=pad)
         else:
             with torch.no_grad():
                 self.comm.broadcast_(self._buffer_list, 0)
@@ -225,9 +291,22 @@ class DistributedDataParallel(nn.Module):
                 eng.xg_slot = slot
 
     # ------------------------------------------------------------------ forward
+    def _to_device(self, obj):
+        """torch DDP moves the inputs to ``device_ids[0]`` (``_to_kwargs``); same here for (nested) tensors."""
+        if isinstance(obj, torch.Tensor):
+            return obj.to(self.device, non_blocking=True) if obj.device != self.device else obj
+        if isinstance(obj, (list, tuple)):
+            return type(obj)(self._to_device(o) for o in obj)
+        if isinstance(obj, dict):
+            return {k: self._to_device(v) for k, v in obj.items()}
+        return obj
+
     def forward(self, *inputs, **kwargs):
+        if self.device.type == "cuda":
+            inputs, kwargs = self._to_device(inputs), self._to_device(kwargs)
         grad_mode = torch.is_grad_enabled()
-        if grad_mode and self.module.training:
+        training_fwd = grad_mode and self.module.training
+        if training_fwd:
             if self.require_backward_grad_sync:
                 _lib.lib().b2_reducer_reset(self._reducer)
                 self._callback_queued = False
@@ -235,9 +314,32 @@ class DistributedDataParallel(nn.Module):
                 self._in_backward_iteration = True
                 self._ready_ids = set()
                 self.comm.begin_backward()
-            if self.broadcast_buffers:
+                self._trim_log()
+            if self._buffer_sync_pending:
+                # a buffer broadcast of the previous forward may still be in flight on the communication stream
+                # (only when no backward ran in between: backward's finalize already joined the streams)
+                torch.cuda.current_stream(self.device).wait_stream(self.comm.stream)
+                self._buffer_sync_pending = False
+            if self.broadcast_buffers and not (self._post_forward_sync and self._buffers_in_sync):
                 self._sync_buffers()
-        return self.module(*inputs, **kwargs)
+        out = self.module(*inputs, **kwargs)
+        if training_fwd and self.broadcast_buffers and self._post_forward_sync and self.world > 1 \
+                and self._buffers_flat is not None:
+            # K3, moved off the critical path: the running statistics this forward just updated are broadcast from
+            # rank 0 on the communication stream while backward computes, instead of before the next forward on the
+            # compute stream (two device barriers in front of the stem). Every training forward therefore still
+            # starts from rank 0's buffers, as with torch DDP's pre-forward broadcast (reference resnet/main.py:121).
+            self._sync_buffers(stream=self.comm.stream)
+            self._buffers_in_sync = True
+            self._buffer_sync_pending = True
+        return out
+
+    def _trim_log(self):
+        """The collective log only ever needs the current iteration (debug order check, tests)."""
+        log = self.comm.launch_log
+        if len(log) > 4096:
+            del log[:len(log) - 256]
+            self._iter_log_start = min(self._iter_log_start, len(log))
 
     # ------------------------------------------------------------------ reducer hooks
     def _autograd_hook(self, p):
@@ -277,7 +379,15 @@ class DistributedDataParallel(nn.Module):
         if self.world == 1 and sgd is None:
             self.comm.launch_log.append(("allreduce", bucket.index))
             return
+        if self.trace_buckets:
+            self._stamp((bucket.index, "ready"), torch.cuda.current_stream(self.device))
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self.comm.stream.wait_event(ev)
+            self._stamp((bucket.index, "launch"), self.comm.stream)
         self.comm.allreduce_bucket(bucket, sgd=sgd)
+        if self.trace_buckets:
+            self._stamp((bucket.index, "done"), self.comm.stream)
         if sgd is not None:
             opt.note_bucket_updated(bucket)
 
@@ -285,15 +395,16 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._in_backward_iteration = False
         left = _lib.lib().b2_reducer_unlaunched(self._reducer)
-        if self.measure_exposed and self.backend == "p2p":
-            # exposed communication = how long the reductions outlast backward's own kernels
-            ev_c, ev_m = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            ev_c.record(torch.cuda.current_stream(self.device))
-            ev_m.record(self.comm.stream)
-            self._exposed_events.append((ev_c, ev_m))
-            if len(self._exposed_events) > 512:
-                self._exposed_events = self._exposed_events[-256:]
+        if self._ts_compute is not None:
+            # exposed communication = how long the reductions outlast backward's own kernels (device clock)
+            L = _lib.lib()
+            L.b2_timestamp(ctypes.c_void_p(self._ts_compute.data_ptr()), self._ts_cap,
+                           ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+            L.b2_timestamp(ctypes.c_void_p(self._ts_comm.data_ptr()), self._ts_cap,
+                           ctypes.c_void_p(self.comm.stream.cuda_stream))
+            _lib.count_launch(2)
         self.comm.finalize()
+        self._buffer_sync_pending = False
         if self._fused_args is not None:
             self.store.mark_params_updated_natively()
         if self._watchdog:
@@ -331,13 +442,102 @@ class DistributedDataParallel(nn.Module):
             self.require_backward_grad_sync = old
 
     def exposed_comm_ms(self, last=None):
-        """Mean time per step by which the gradient reductions outlasted backward compute (device events)."""
-        if not self._exposed_events:
+        """Mean time per step by which the gradient reductions outlasted backward compute, from device-side
+        timestamps (valid for eager steps and for CUDA-graph replays alike). ``last``: only the most recent N steps
+        (at most 256 are kept)."""
+        if self._ts_compute is None:
             return 0.0 if self.world == 1 else None
         torch.cuda.synchronize(self.device)
-        evs = self._exposed_events[-last:] if last else self._exposed_events
-        vals = [max(0.0, c.elapsed_time(m)) for c, m in evs]
+        tc, tm = self._ts_compute.cpu(), self._ts_comm.cpu()
+        n = int(min(tc[0].item(), tm[0].item()))
+        if n == 0:
+            return None
+        k = min(n, self._ts_cap, last or self._ts_cap)
+        vals = []
+        for i in range(n - k, n):
+            a, b = int(tc[1 + i % self._ts_cap]), int(tm[1 + i % self._ts_cap])
+            vals.append(max(0.0, (b - a) / 1e6))
         return sum(vals) / len(vals)
+
+    def reset_exposed_comm(self):
+        if self._ts_compute is not None:
+            self._ts_compute.zero_()
+            self._ts_comm.zero_()
+
+    # ------------------------------------------------------------------ per-bucket trace (B200DDP_TRACE=1)
+    def _stamp(self, key, stream):
+        ring = self._bucket_rings.get(key)
+        if ring is None:
+            ring = self._bucket_rings[key] = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
+        _lib.lib().b2_timestamp(ctypes.c_void_p(ring.data_ptr()), self._ts_cap, ctypes.c_void_p(stream.cuda_stream))
+        _lib.count_launch()
+
+    def bucket_trace(self):
+        """Per-bucket ``ready`` (compute stream: its last gradient was written), ``launch`` (communication stream
+        reached the reduction) and ``done`` times of the most recent step in microseconds relative to the first
+        bucket's ready time, plus the end of backward compute. Needs ``B200DDP_TRACE=1`` (three marker kernels per
+        bucket, also inside graph replays). The flight-recorder view of ProcessGroupNCCL, per bucket."""
+        if not self._bucket_rings:
+            return None
+        torch.cuda.synchronize(self.device)
+
+        def last(ring):
+            r = ring.cpu()
+            n = int(r[0])
+            return int(r[1 + (n - 1) % self._ts_cap]) if n else None
+
+        rows, t0 = [], None
+        for b in self.store.buckets:
+            ent = {k: last(self._bucket_rings[(b.index, k)]) for k in ("ready", "launch", "done")
+                   if (b.index, k) in self._bucket_rings}
+            if ent.get("ready") is not None and t0 is None:
+                t0 = ent["ready"]
+            rows.append((b.index, b.numel * 4, ent))
+        out = [{"bucket": i, "bytes": nb, **{k: (v - t0) / 1e3 for k, v in ent.items() if v is not None}}
+               for i, nb, ent in rows]
+        end = last(self._ts_compute) if self._ts_compute is not None else None
+        return {"buckets": out, "backward_end_us": (end - t0) / 1e3 if end and t0 else None}
+
+    # ------------------------------------------------------------------ teardown
+    def close(self):
+        """Release the symmetric window of this wrapper (P2P backend). The module stays usable: its buffers are
+        moved back to ordinary device memory and gradients that live in the window are dropped first."""
+        if self._closed:
+            return
+        self._closed = True
+        if self.backend != "p2p":
+            return
+        torch.cuda.synchronize(self.device)
+        with torch.no_grad():
+            if self._buffers_flat is not None:
+                for mod in self.module.modules():
+                    for bname, b in list(mod._buffers.items()):
+                        if b is not None and b.is_cuda:
+                            mod._buffers[bname] = b.clone()
+            for p in self.ordered_params:
+                p.grad = None
+        for b in self.store.buckets:
+            b.g32 = torch.zeros(0, dtype=torch.float32, device=self.device)
+            if hasattr(b, "wire16"):
+                b.wire16 = None
+        self._buffers_flat = None
+        self._buffer_list = [b for b in self.module.buffers()]
+        self.comm._stage = None
+        if hasattr(self.module, "_b2_xgpu_ctx"):
+            self.module._b2_xgpu_ctx = None
+            eng = getattr(self.module, "_engine", None)
+            if eng is not None:
+                eng.xg = None
+        self.xgpu_compute_ctx = None
+        self.store.on_ready = None
+        for h in self._hooks:
+            h.remove()
+        self.comm.window.close()
+
+    def load_state_dict(self, state_dict, strict=True, **kw):
+        out = super().load_state_dict(state_dict, strict=strict, **kw)
+        self._buffers_in_sync = False    # ranks may have loaded different files: the next forward syncs first
+        return out
 
     # ------------------------------------------------------------------ introspection
     def bucket_sizes(self):

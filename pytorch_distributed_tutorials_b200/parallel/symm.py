@@ -7,6 +7,7 @@ multicast transport, UNIX-socket names over which file descriptors are passed).
 """
 import ctypes
 import os
+import weakref
 
 import torch
 import torch.distributed as dist
@@ -34,6 +35,41 @@ def _check(err, what):
         raise RuntimeError("%s failed (error %d)" % (what, err))
 
 
+def _release(res):
+    """Undo everything a window's set-up created (``res`` is the plain dict of raw handles and addresses, so this
+    can run from a ``weakref.finalize`` after the window object itself is gone). Local only - no collectives: a
+    peer that still maps this rank's memory keeps the physical pages alive through its own imported handle."""
+    if res.get("released"):
+        return
+    res["released"] = True
+    try:
+        L = _lib.lib()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize(res["device"])
+        nbytes = ctypes.c_longlong(res["nbytes"])
+        if res["transport"] == "vmm":
+            if res.get("mc_handle") is not None:
+                if res.get("mc_bound"):
+                    L.b2_mc_unbind(ctypes.c_ulonglong(res["mc_handle"]), res["device"], nbytes)
+                if res.get("mc_ptr"):
+                    L.b2_vmm_unmap(ctypes.c_void_p(res["mc_ptr"]), nbytes)
+                L.b2_vmm_release(ctypes.c_ulonglong(res["mc_handle"]))
+            for ptr_, h in res.get("peers", []):
+                L.b2_vmm_unmap(ctypes.c_void_p(ptr_), nbytes)
+                L.b2_vmm_release(ctypes.c_ulonglong(h))
+            if res.get("local_ptr"):
+                L.b2_vmm_unmap(ctypes.c_void_p(res["local_ptr"]), nbytes)
+            if res.get("local_handle") is not None:
+                L.b2_vmm_release(ctypes.c_ulonglong(res["local_handle"]))
+        elif res["transport"] == "ipc":
+            for ptr_, _ in res.get("peers", []):
+                L.b2_ipc_close(ctypes.c_void_p(ptr_))
+            if res.get("local_ptr"):
+                L.b2_ipc_free(ctypes.c_void_p(res["local_ptr"]))
+    except Exception:  # noqa: BLE001  (interpreter shutdown: the driver reclaims everything anyway)
+        pass
+
+
 class SymmetricWindow:
     def __init__(self, nbytes, device, group=None, transport=None):
         self.group = group
@@ -47,6 +83,10 @@ class SymmetricWindow:
         self._cursor = HEADER_BYTES
         L = _lib.lib()
         torch.cuda.set_device(self.device)
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        # raw resources, released by close() or, when the last tensor aliasing the window is gone, by the finalizer
+        self._res = {"transport": None, "device": dev_index, "nbytes": 0, "peers": [], "local_ptr": None,
+                     "local_handle": None, "mc_handle": None, "mc_ptr": None, "mc_bound": False}
         nbytes = (int(nbytes) + HEADER_BYTES + (2 << 20) - 1) // (2 << 20) * (2 << 20)
         self.nbytes = nbytes
         self.ptrs = [0] * self.world
@@ -73,7 +113,23 @@ class SymmetricWindow:
             self.transport = "vmm"
         self.epochs = torch.zeros(N_PADS * CHANNELS, dtype=torch.int32, device=self.device)
         self._ctx_cache = {}
+        self._res.update(transport=self.transport, nbytes=self.nbytes, local_ptr=self.local_ptr, mc_ptr=self.mc_ptr)
+        self._finalizer = weakref.finalize(self, _release, self._res)
         dist.barrier(group=group)
+
+    @property
+    def closed(self):
+        return bool(self._res.get("released"))
+
+    def close(self):
+        """Release the window: multicast unbind, unmap + address-range free of every mapping (own, peers',
+        multicast), release of every handle (``cuMemRelease``), or ``cudaIpcCloseMemHandle`` / ``cudaFree`` for
+        the IPC transport. Every tensor that aliases the window is invalid afterwards (``DistributedDataParallel
+        .close()`` moves the module's buffers and gradients out first). Local operation; idempotent. Without an
+        explicit call the same happens when the last tensor aliasing the window is garbage-collected."""
+        self._finalizer()
+        self.mc_ptr = None
+        self._ctx_cache = {}
 
     # ------------------------------------------------------------------ transports
     def _setup_ipc(self, L):
@@ -81,6 +137,7 @@ class SymmetricWindow:
         h = (ctypes.c_ubyte * 64)()
         _check(L.b2_ipc_alloc(ctypes.c_longlong(self.nbytes), ctypes.byref(p), h), "b2_ipc_alloc")
         self.local_ptr = p.value
+        self._res.update(transport="ipc", nbytes=self.nbytes, local_ptr=self.local_ptr)
         handles = [None] * self.world
         dist.all_gather_object(handles, bytes(h), group=self.group)
         for r in range(self.world):
@@ -91,6 +148,7 @@ class SymmetricWindow:
                 hb = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
                 _check(L.b2_ipc_open(hb, ctypes.byref(q)), "b2_ipc_open(rank %d)" % r)
                 self.ptrs[r] = q.value
+                self._res["peers"].append((q.value, 0))
 
     def _setup_vmm(self, L):
         L.b2_vmm_round.restype = ctypes.c_longlong
@@ -105,6 +163,7 @@ class SymmetricWindow:
         _check(L.b2_vmm_alloc(ctypes.c_longlong(self.nbytes), dev, ctypes.byref(p), ctypes.byref(mh),
                               ctypes.byref(fd)), "b2_vmm_alloc")
         self.local_ptr = p.value
+        self._res.update(transport="vmm", nbytes=self.nbytes, local_ptr=self.local_ptr, local_handle=mh.value)
         want_mc = bool(L.b2_vmm_multicast_supported(dev)) and os.environ.get("B200DDP_NVLS", "1") == "1"
         fds = [fd.value]
         mc_handle = ctypes.c_ulonglong()
@@ -136,9 +195,12 @@ class SymmetricWindow:
             if pfd < 0:
                 raise RuntimeError("fetching the window descriptor of rank %d failed (%d)" % (r, pfd))
             q = ctypes.c_void_p()
-            _check(L.b2_vmm_import(pfd, ctypes.c_longlong(self.nbytes), dev, ctypes.byref(q)), "b2_vmm_import")
+            ph = ctypes.c_ulonglong()
+            _check(L.b2_vmm_import_h(pfd, ctypes.c_longlong(self.nbytes), dev, ctypes.byref(q), ctypes.byref(ph)),
+                   "b2_vmm_import_h")
             L.b2_fd_close(pfd)
             self.ptrs[r] = q.value
+            self._res["peers"].append((q.value, ph.value))
         if want_mc:
             if self.rank != 0:
                 mfd = L.b2_fd_fetch(info[0][0].encode(), 1, 30000)
@@ -146,12 +208,16 @@ class SymmetricWindow:
                     raise RuntimeError("fetching the multicast descriptor failed (%d)" % mfd)
                 _check(L.b2_mc_import(mfd, ctypes.byref(mc_handle)), "b2_mc_import")
                 L.b2_fd_close(mfd)
+            self._res["mc_handle"] = mc_handle.value
             _check(L.b2_mc_add_device(mc_handle, dev), "b2_mc_add_device")
             dist.barrier(group=self.group)  # every device added before anyone binds
             mp = ctypes.c_void_p()
             _check(L.b2_mc_bind_and_map(mc_handle, mh, ctypes.c_longlong(self.nbytes), dev, ctypes.byref(mp)),
                    "b2_mc_bind_and_map")
             self.mc_ptr = mp.value
+            self._res.update(mc_ptr=mp.value, mc_bound=True)
+        elif self.rank == 0 and len(fds) == 2:
+            self._res["mc_handle"] = mc_handle.value   # created but not used by every rank: still to be released
         srv.join(timeout=30)
         L.b2_fd_close(sock)
         for f in fds:

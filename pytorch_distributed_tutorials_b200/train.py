@@ -129,6 +129,12 @@ def main(argv=None):
                 print("-" * 75)
                 print("Epoch: {}, Accuracy: {}".format(epoch, acc))
                 print("-" * 75, flush=True)
+            if dist.is_initialized() and dist.get_world_size() > 1:
+                # The other ranks wait here, on the host, for rank 0's evaluation + checkpoint (the reference makes
+                # them wait inside their first NCCL collective instead, resnet/main.py:109-115). A CPU-tensor
+                # all-reduce always travels over the gloo control plane; it is bounded by the process-group timeout
+                # and keeps the ranks out of the device-side spin loops while nothing can answer them.
+                dist.all_reduce(torch.zeros(1))
         ddp_model.train()
         if args.reshuffle_each_epoch:
             train_sampler.set_epoch(epoch)

@@ -11,8 +11,10 @@ epochs, momentum), so replays need no host bookkeeping.
     for x, y in loader:
         loss = step(x, y)          # loss: device scalar, valid until the next call
 
-Hyper-parameters are baked into the captured kernels' arguments; the step re-captures itself when the learning
-rate, momentum or weight decay of the optimizer changes (epoch-level schedules cost one capture per change).
+Hyper-parameters: the native SGD kernels (stand-alone and as the all-reduce epilogue) read learning rate, momentum
+and weight decay from a three-float device block owned by the optimizer (``optim.SGD.hyper_dev``), refreshed before
+every replay, so per-step learning-rate schedules cost one tiny host->device copy and never a re-capture.  Only a
+stock optimizer (values baked into its kernels' arguments) makes the step re-capture itself on a change.
 """
 import warnings
 
@@ -46,14 +48,23 @@ class GraphedTrainStep:
 
     def _capture(self, x, y):
         ddp = self.model
-        old_measure = getattr(ddp, "measure_exposed", False)
         old_watchdog = getattr(ddp, "_watchdog", False)
-        if hasattr(ddp, "measure_exposed"):
-            ddp.measure_exposed = False      # timing events cannot be recorded inside a capture
-            ddp._watchdog = False
+        if hasattr(ddp, "_watchdog"):
+            ddp._watchdog = False            # the watchdog's event cannot be recorded inside a capture
         sx, sy = torch.empty_like(x), torch.empty_like(y)
         sx.copy_(x)
         sy.copy_(y)
+        # input pointer slot: the stem kernel of our ResNets reads the batch through a device-side pointer, so a
+        # replay consumes the caller's tensor in place (e.g. the buffer the DevicePrefetcher's host->device copy
+        # landed in) instead of a copy in a static buffer - 154 MB less traffic per step for ImageNet-shaped fp32
+        root = getattr(ddp, "module", ddp)
+        slot = None
+        if hasattr(root, "_b2_input_slot") and x.is_contiguous() and x.dtype in (torch.float32, torch.bfloat16):
+            from ..ops import native
+            slot = torch.zeros(1, dtype=torch.int64, device=x.device)
+            native.set_ptr_slot(slot, sx)
+            root._b2_input_slot = slot
+            root._b2_input_slot_used = False
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         n0 = _lib.launches()
@@ -65,12 +76,15 @@ class GraphedTrainStep:
                 loss.backward()
                 self.optimizer.step()
         finally:
-            if hasattr(ddp, "measure_exposed"):
-                ddp.measure_exposed = old_measure
+            if slot is not None:
+                root._b2_input_slot = None
+                if not getattr(root, "_b2_input_slot_used", False):
+                    slot = None              # this input shape went through a path that reads the tensor directly
+            if hasattr(ddp, "_watchdog"):
                 ddp._watchdog = old_watchdog
         self.captures += 1
         return {"graph": g, "x": sx, "y": sy, "loss": loss.detach(), "hyper": self._hyper(),
-                "launches": _lib.launches() - n0}
+                "launches": _lib.launches() - n0, "slot": slot}
 
     def __call__(self, x, y):
         if not self.enabled or not x.is_cuda:
@@ -82,8 +96,11 @@ class GraphedTrainStep:
             return self._eager(x, y)
         key = (tuple(x.shape), x.dtype, tuple(y.shape), bool(self.model.training))
         entry = self._graphs.get(key)
-        if entry is not None and entry["hyper"] != self._hyper():
-            entry = None                       # learning rate (or momentum / weight decay) changed: re-capture
+        dev_hyper = getattr(self.optimizer, "hyper_dev", None) is not None and self.optimizer._native_ok()
+        if dev_hyper:
+            self.optimizer.hyper_dev(x.device)   # refresh the device-side {lr, momentum, weight_decay} block
+        elif entry is not None and entry["hyper"] != self._hyper():
+            entry = None                       # stock optimizer: values are baked into the capture -> re-capture
         if entry is None:
             try:
                 entry = self._capture(x, y)
@@ -96,7 +113,16 @@ class GraphedTrainStep:
                 return self._eager(x, y)
             self._graphs[key] = entry
             # the capture itself does not execute anything: fall through to the first replay
-        entry["x"].copy_(x, non_blocking=True)
+        slot = entry.get("slot")
+        if slot is not None and x.is_contiguous() and x.dtype == entry["x"].dtype:
+            from ..ops import native
+            native.set_ptr_slot(slot, x)            # the replay reads this batch where it is
+            self._keep = x                          # until the next call: the replay's first kernel reads it
+        else:
+            entry["x"].copy_(x, non_blocking=True)
+            if slot is not None:
+                from ..ops import native
+                native.set_ptr_slot(slot, entry["x"])
         entry["y"].copy_(y, non_blocking=True)
         entry["graph"].replay()
         _lib.count_launch(entry["launches"])   # kernels of ours that one replay runs

@@ -21,6 +21,8 @@ def free_port():
 def _entry(rank, world, port, fn, backend, args, q):
     os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
                        "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank)})
+    # a protocol bug must fail a test within a minute, not sit in a spin loop for the 30-minute production default
+    os.environ.setdefault("B200DDP_SPIN_TIMEOUT_MS", "60000")
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
     try:

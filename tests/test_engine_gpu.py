@@ -80,6 +80,71 @@ def test_resnet50_full_depth_sane():
         assert 0.3 * b <= a <= 3.0 * b + 1e-6, (n, a, b)
 
 
+def test_eval_mode_with_grad_uses_running_statistics_in_backward():
+    """model.eval() with grad enabled (frozen-BN fine-tuning, saliency / input gradients): BatchNorm normalises with
+    its running statistics, and so must its backward. The engine only implements the training-mode backward, so
+    such a forward is routed through the stock autograd path - gradients must equal the oracle's, not silently be
+    the training-mode formula on stale batch statistics."""
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    torch.manual_seed(5)
+    m = resnet18().to(DEV)
+    x = torch.randn(8, 3, 32, 32, device=DEV)
+    y = torch.randint(0, 1000, (8,), device=DEV)
+    m.train()
+    m(x).sum().backward()          # leaves batch statistics of THIS batch in the engine's saved state
+    m.zero_grad()
+    ref = copy.deepcopy(m)
+    m.eval()
+    ref.eval()
+    x2 = torch.randn(8, 3, 32, 32, device=DEV, requires_grad=True)
+    x2r = x2.detach().clone().requires_grad_(True)
+    nn.functional.cross_entropy(m(x2), y).backward()
+    nn.functional.cross_entropy(ref.forward_reference(x2r), y).backward()
+    assert _cos(x2.grad, x2r.grad) > 0.999
+    for (n, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
+        assert p.grad is not None and torch.allclose(p.grad, q.grad, rtol=1e-3, atol=1e-5), n
+    # frozen single layers inside a training model take the same route
+    m.train()
+    m.layer1[0].bn1.eval()
+    ref.train()
+    ref.layer1[0].bn1.eval()
+    m.zero_grad()
+    ref.zero_grad()
+    nn.functional.cross_entropy(m(x), y).backward()
+    nn.functional.cross_entropy(ref.forward_reference(x), y).backward()
+    assert torch.allclose(m.layer1[0].bn1.weight.grad, ref.layer1[0].bn1.weight.grad, rtol=1e-3, atol=1e-5)
+
+
+def test_learning_rate_schedule_does_not_recapture_the_graph():
+    """The native SGD kernels read lr / momentum / weight decay from a device block: changing the learning rate
+    every step keeps ONE captured graph, and the weights equal an eager run with the same schedule bit for bit."""
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    from pytorch_distributed_tutorials_b200.utils.graph import GraphedTrainStep
+    torch.manual_seed(6)
+    base = resnet18().to(DEV)
+    twin = copy.deepcopy(base)
+    x = torch.randn(16, 3, 32, 32, device=DEV)
+    y = torch.randint(0, 10, (16,), device=DEV)
+    out = []
+    for net, graph in ((base, True), (twin, False)):
+        ddp = DistributedDataParallel(net, device_ids=[0])
+        opt = optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
+        sched = torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.7)
+        step = GraphedTrainStep(ddp, CrossEntropyLoss(), opt, warmup=2, enabled=graph)
+        for _ in range(7):
+            step(x, y)
+            sched.step()
+        torch.cuda.synchronize()
+        out.append(([p.detach().clone() for p in ddp.parameters()], step.captures, opt.param_groups[0]["lr"]))
+    (pg, caps, lr_g), (pe, _, lr_e) = out
+    assert caps == 1, caps
+    assert abs(lr_g - 0.05 * 0.7 ** 7) < 1e-9 and lr_g == lr_e
+    assert all(torch.equal(a, b) for a, b in zip(pg, pe))
+
+
 def test_eval_mode_and_no_grad():
     from pytorch_distributed_tutorials_b200.models.resnet import resnet18
     torch.manual_seed(1)

@@ -25,6 +25,10 @@ CONV_SHAPES = [  # ci, co, k, s, p, H, N
     (64, 64, 1, 1, 0, 56, 4), (64, 64, 3, 1, 1, 56, 4), (256, 128, 1, 1, 0, 56, 2), (128, 128, 3, 2, 1, 56, 2),
     (256, 512, 1, 2, 0, 56, 2), (512, 2048, 1, 1, 0, 7, 8), (512, 512, 3, 1, 1, 7, 8), (1024, 256, 1, 1, 0, 14, 4),
     (64, 128, 3, 2, 1, 8, 8), (512, 512, 3, 1, 1, 1, 8), (256, 512, 1, 2, 0, 2, 8), (128, 256, 3, 2, 1, 28, 3),
+    # the benchmark's own batch (256 per GPU): persistent-kernel tile loops, split-K plans and statistics warps at
+    # the sizes that are timed - 1x1 64->256 @56, 3x3 256 @14, strided 3x3 128 @56, strided 1x1 256->512 @56
+    (64, 256, 1, 1, 0, 56, 256), (256, 256, 3, 1, 1, 14, 256), (128, 128, 3, 2, 1, 56, 256),
+    (256, 512, 1, 2, 0, 56, 256),
 ]
 
 

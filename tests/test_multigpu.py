@@ -14,12 +14,15 @@ def _need(n):
         pytest.skip("needs %d GPUs" % n)
 
 
-def _collectives(rank, world):
+def _collectives(rank, world, skew_us=0):
     import torch.distributed as dist
     from pytorch_distributed_tutorials_b200.parallel.comm import P2PComm
     from pytorch_distributed_tutorials_b200.parallel.flat import Bucket
     dev = torch.device("cuda", rank)
     comm = P2PComm(dev, None, 600 << 20)
+    # skew injection: a pseudo-random subset of the CTAs sleeps before / between the phases of every collective
+    # kernel, so a kernel that consumes what a differently-numbered CTA of a peer produced reads stale data
+    comm.set_debug_skew_us(skew_us)
     res = {"transport": comm.window.transport, "multicast": bool(comm.mc_base)}
     sizes = [128, 4096, 129 * 1024, 513000 + 24, 7213056, 25 * 1024 * 1024 // 4]
     algos = ["oneshot", "twoshot"] + (["multimem"] if comm.mc_base else [])
@@ -54,29 +57,48 @@ def _collectives(rank, world):
             dist.broadcast(other, 0)
             res["%s_%d_ident" % (algo, n)] = bool(torch.equal(mine, other))
             dist.barrier()
-        # fused SGD epilogue vs unfused torch math (two steps: first-step buffer init, then momentum)
-        p = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(7))
-        b.p32, b.mom = p.clone(), torch.zeros(n, device=dev)
-        b.shadow = torch.empty(n, device=dev, dtype=torch.bfloat16)
-        pr, mr = p.clone(), None
-        for step in range(2):
-            g = torch.Generator(device=dev).manual_seed(31 * rank + step)
-            local = torch.randn(n, device=dev, generator=g)
-            b.g32.copy_(local)
-            avg = local.clone()
-            dist.all_reduce(avg)
-            avg /= world
-            gg = avg + 1e-5 * pr
-            mr = gg.clone() if mr is None else 0.9 * mr + gg
-            pr = pr - 0.01 * mr
-            torch.cuda.synchronize()
-            dist.barrier()
-            comm.allreduce_bucket(b, sgd=(0.01, 0.9, 1e-5, step == 0), algo="twoshot" if n > 4096 else "oneshot")
-            comm.finalize()
-            torch.cuda.synchronize()
-        res["sgd_%d" % n] = (b.p32 - pr).abs().max().item()
-        res["sgd_%d_shadow" % n] = bool(torch.equal(b.shadow, b.p32.to(torch.bfloat16)))
-        res["sgd_%d_grad" % n] = (b.g32 - avg).abs().max().item()
+        # fused SGD epilogue vs unfused torch math (two steps: first-step buffer init, then momentum), with every
+        # algorithm that can carry it - multimem is the default for world > 2 (B2_AR_AUTO)
+        sgd_algos = ["twoshot" if n > 4096 else "oneshot"] + (["multimem"] if comm.mc_base and n * 4 >= 32768 else [])
+        for wire in ("fp32", "bf16"):
+            comm.wire = wire
+            for algo in sgd_algos:
+                p = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(7))
+                b.p32, b.mom = p.clone(), torch.zeros(n, device=dev)
+                b.shadow = torch.empty(n, device=dev, dtype=torch.bfloat16)
+                pr, mr = p.clone(), None
+                for step in range(2):
+                    g = torch.Generator(device=dev).manual_seed(31 * rank + step)
+                    local = torch.randn(n, device=dev, generator=g)
+                    b.g32.copy_(local)
+                    if wire == "fp32":
+                        avg = local.clone()
+                        dist.all_reduce(avg)
+                        avg /= world
+                    else:
+                        parts = [torch.empty_like(local) for _ in range(world)]
+                        dist.all_gather(parts, local)
+                        acc = torch.zeros_like(local)
+                        for q in parts:
+                            acc += q.to(torch.bfloat16).float()
+                        avg = (acc / world).to(torch.bfloat16).float()
+                    gg = avg + 1e-5 * pr
+                    mr = gg.clone() if mr is None else 0.9 * mr + gg
+                    pr = pr - 0.01 * mr
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    comm.allreduce_bucket(b, sgd=(0.01, 0.9, 1e-5, step == 0), algo=algo)
+                    comm.finalize()
+                    torch.cuda.synchronize()
+                tag = "sgd%s_%s_%d" % ("16" if wire == "bf16" else "", algo, n)
+                res[tag] = (b.p32 - pr).abs().max().item()
+                res[tag + "_shadow"] = bool(torch.equal(b.shadow, b.p32.to(torch.bfloat16)))
+                res[tag + "_grad"] = (b.g32 - avg).abs().max().item()
+                mine = b.p32.clone()
+                other = mine.clone()
+                dist.broadcast(other, 0)
+                res[tag + "_ident"] = bool(torch.equal(mine, other))
+        comm.wire = "fp32"
     # bf16 wire format: fp32 accumulation of bf16-rounded inputs in rank order, rounded to bf16 once
     comm16 = comm
     comm16.wire = "bf16"
@@ -112,18 +134,27 @@ def _collectives(rank, world):
     return res
 
 
-@pytest.mark.parametrize("world", [2, 4, 8])
-def test_p2p_collectives_match_nccl(world):
+@pytest.mark.parametrize("world,skew_us", [(2, 0), (2, 300), (4, 300), (8, 300)])
+def test_p2p_collectives_match_nccl(world, skew_us):
+    """skew_us > 0: same checks with CTAs of one rank pushed far apart in progress (csrc/xgpu.cuh debug_skew) - the
+    cross-CTA race of the multimem reduce+SGD kernel found in review passes the skew-free run by lock-step luck."""
     _need(world)
-    out = run_ranks(_collectives, world=world, backend="b200", timeout=600)
+    out = run_ranks(_collectives, world=world, backend="nccl", args=(skew_us,), timeout=900)
     for r in out:
         for k, v in r.items():
             if k.endswith("_ident") or k.endswith("_shadow") or k == "bcast":
                 assert v is True, (k, r)
             elif k.startswith(("oneshot", "twoshot", "multimem")):
                 assert v < 1e-5, (k, v)
-            elif k.startswith("sgd_"):
-                assert v < 1e-5, (k, v)
+            elif k.startswith("sgd"):
+                # fp32 wire: exact up to fp32 rounding; bf16 wire (values pre-scaled): the averaged gradient may
+                # differ by one bf16 ulp where the in-switch reduction order differs from the reference order
+                if k.startswith("sgd_"):
+                    assert v < 1e-5, (k, v)
+                elif k.endswith("_grad"):
+                    assert v < 5e-2, (k, v)          # one bf16 ulp of an O(1) gradient
+                else:
+                    assert v < 2e-3, (k, v)          # lr * (1 + mu + 1) * one ulp
             elif k.startswith("bf16wire_"):
                 assert v < 1e-2, (k, v)      # at most one bf16 ulp (multimem's in-switch order may differ)
 
@@ -176,17 +207,21 @@ def _ddp_train(rank, world, sync_bn):
     dist.broadcast(other, 0)
     log = ours.collective_log()
     return {"ours": l1s, "theirs": l2s, "ident": bool(torch.equal(flat, other)), "backend": ours.backend,
-            "n_allreduce": len([c for c in log if c[0] == "allreduce"]), "exposed": ours.exposed_comm_ms()}
+            "n_allreduce": len([c for c in log if c[0] == "allreduce"]), "exposed": ours.exposed_comm_ms(),
+            "buckets": ours.bucket_sizes()}
 
 
-@pytest.mark.parametrize("sync_bn", [False, True])
-def test_ddp_p2p_trains_like_torch_ddp(sync_bn):
-    _need(2)
-    out = run_ranks(_ddp_train, world=2, backend="b200", args=(sync_bn,), timeout=600)
+@pytest.mark.parametrize("world,sync_bn", [(2, False), (2, True), (4, False), (8, False), (8, True)])
+def test_ddp_p2p_trains_like_torch_ddp(world, sync_bn):
+    _need(world)
+    out = run_ranks(_ddp_train, world=world, backend="nccl", args=(sync_bn,), timeout=600)
     for r in out:
         assert r["backend"] == "p2p"
         assert r["ident"], "replicas drifted apart"
-        assert r["n_allreduce"] == 15
+        # torch's three ResNet-18 buckets, the last one cut once more so that only <= 1 MiB waits for the end of backward
+        assert r["buckets"][:2] == [513000, 7213056] and len(r["buckets"]) == 4 and r["buckets"][3] * 4 <= 1 << 20, r
+        assert r["n_allreduce"] == 5 * 4
+        assert r["exposed"] is not None and r["exposed"] >= 0.0
         assert r["ours"][-1] < r["ours"][0]
         assert abs(r["ours"][0] - r["theirs"][0]) < 0.05 * r["theirs"][0], r
         assert abs(r["ours"][-1] - r["theirs"][-1]) < 0.35 * max(r["theirs"][-1], 0.5), r
@@ -235,7 +270,7 @@ def _syncbn_stats(rank, world):
 
 def test_syncbn_in_kernel_stats_match_torch():
     _need(2)
-    outs = run_ranks(_syncbn_stats, world=2, backend="b200", timeout=600)
+    outs = run_ranks(_syncbn_stats, world=2, backend="nccl", timeout=600)
     for r in outs:
         for k, v in r.items():
             assert v < 3e-2, (k, v, r)
@@ -264,21 +299,25 @@ def _graph_ddp(rank, world):
         losses = [float(step(xs[i % 2], ys[i % 2]).item()) for i in range(7)]
         torch.cuda.synchronize()
         dist.barrier()
-        out.append((losses, torch.cat([p.detach().reshape(-1) for p in ddp.parameters()]).clone(), step.captures))
-    (lg, pg, caps), (le, pe, _) = out
+        out.append((losses, torch.cat([p.detach().reshape(-1) for p in ddp.parameters()]).clone(), step.captures,
+                    ddp.exposed_comm_ms(last=3)))
+    (lg, pg, caps, exposed), (le, pe, _, _) = out
     other = pg.clone()
     dist.broadcast(other, 0)
     return {"captures": caps, "same_as_eager": bool(torch.equal(pg, pe)), "ident": bool(torch.equal(pg, other)),
-            "lg": lg, "le": le}
+            "lg": lg, "le": le, "exposed": exposed}
 
 
-def test_graph_captured_step_with_p2p_allreduce_matches_eager():
-    _need(2)
-    outs = run_ranks(_graph_ddp, world=2, backend="b200", timeout=600)
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_graph_captured_step_with_p2p_allreduce_matches_eager(world):
+    _need(world)
+    outs = run_ranks(_graph_ddp, world=world, backend="b200", timeout=600)   # gloo control plane: no NCCL at all
     for r in outs:
         assert r["captures"] == 1
         assert r["ident"], "replicas drifted apart under graph replay"
         assert r["same_as_eager"], (r["lg"], r["le"])
+        # exposed communication is measured by device timestamps inside the replayed graph (not only in eager steps)
+        assert r["exposed"] is not None and 0.0 <= r["exposed"] < 50.0, r["exposed"]
 
 
 def _fault(rank, world):
@@ -371,6 +410,79 @@ def _generic_module(rank, world):
 
 def test_generic_module_through_p2p_backend_matches_torch_ddp():
     _need(2)
-    for r in run_ranks(_generic_module, world=2, backend="b200", timeout=600):
+    for r in run_ranks(_generic_module, world=2, backend="nccl", timeout=600):
         assert r["ident"] and r["buckets"] > 1
         assert r["maxdiff"] < 1e-4, r
+
+
+def _teardown(rank, world):
+    """Construct / destroy the wrapper many times: the symmetric windows (VMM allocations mapped on every peer,
+    multicast binding) must really be released - device memory in use stays flat."""
+    import gc
+    import torch.distributed as dist
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    dev = torch.device("cuda", rank)
+    x = torch.randn(4, 3, 32, 32, device=dev)
+    used = []
+    for it in range(20):
+        net = resnet18().to(dev)
+        ddp = DistributedDataParallel(net, device_ids=[rank])
+        ddp(x).sum().backward()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if it % 2 == 0:
+            ddp.close()                       # explicit
+            rm = net.bn1.running_mean.clone() # the module survives its wrapper: buffers were moved out of the window
+            assert torch.isfinite(rm).all()
+        del ddp, net                          # odd iterations: garbage collection alone must release the window
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
+        free, total = torch.cuda.mem_get_info(dev)
+        used.append((total - free) >> 20)
+    return {"used_mib": used}
+
+
+def test_symmetric_windows_are_released():
+    _need(2)
+    for r in run_ranks(_teardown, world=2, backend="b200", timeout=600):
+        u = r["used_mib"]
+        # one window is ~200 MiB (x2 for the peer mapping's physical pages being kept alive): a leak of 20 shows
+        assert max(u[4:]) - min(u[4:]) < 96, u
+
+
+def _slow_rank0(rank, world):
+    """Rank 0 is busy for 25 s before a step (the reference evaluates the whole test set and writes the checkpoint
+    on rank 0 alone, resnet/main.py:109-115) while rank 1 already sits in the step's first collective. With the
+    default device-side spin bound (30 min, as NCCL's process-group timeout) nothing traps."""
+    import os
+    import time
+    os.environ.pop("B200DDP_SPIN_TIMEOUT_MS", None)
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    ddp = DistributedDataParallel(resnet18().to(dev), device_ids=[rank])
+    opt = optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9, fuse_with_backward=True)
+    crit = CrossEntropyLoss()
+    x = torch.randn(8, 3, 32, 32, device=dev)
+    y = torch.randint(0, 10, (8,), device=dev)
+    t0 = time.time()
+    for it in range(3):
+        if rank == 0 and it == 1:
+            time.sleep(25)
+        opt.zero_grad()
+        loss = crit(ddp(x), y)
+        loss.backward()
+        opt.step()
+        torch.cuda.synchronize()
+    return {"seconds": time.time() - t0, "loss": float(loss.item())}
+
+
+def test_slow_rank0_does_not_trip_the_spin_bound():
+    _need(2)
+    for r in run_ranks(_slow_rank0, world=2, backend="b200", timeout=300):
+        assert r["seconds"] > 24 and r["loss"] == r["loss"], r
