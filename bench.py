@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying "
                     "the captured whole-step CUDA graph")
     ap.add_argument("--no-comm-probe", action="store_true", help="skip the backward with/without-sync probe")
+    ap.add_argument("--kernel-breakdown", default=None, metavar="FILE",
+                    help="after the timed region, run 3 more steps under torch.profiler (CUPTI) and write rank 0's "
+                         "per-kernel device-time table to FILE (not part of any reported number)")
     ap.add_argument("--reference-strict", action="store_true",
                     help="report the reference as unavailable instead of running the minimally-fixed harness")
     return ap.parse_args()
@@ -366,6 +369,29 @@ def main():
         e2e = {"value": global_batch / (ms_e2e / 1e3), "unit": "images/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                "final_loss": float(loss_host[args.steps - 1])}
+
+    if args.kernel_breakdown:
+        from torch.profiler import ProfilerActivity, profile
+        barrier_sync(world)
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(3):
+                dev_step(i)
+            torch.cuda.synchronize()
+        barrier_sync(world)
+        if rank == 0:
+            rows = [(k.key, k.device_time_total / 3e3, k.count / 3) for k in prof.key_averages()
+                    if k.device_time_total > 0]
+            rows.sort(key=lambda r: -r[1])
+            with open(args.kernel_breakdown, "w") as fh:
+                fh.write("# %s n_gpus=%d model=%s batch=%d: device time per step by kernel (torch.profiler/CUPTI; "
+                         "streams overlap, so the sum exceeds the step time)\n" % (args.impl, world, args.model,
+                                                                                  args.batch))
+                fh.write("total %.3f ms over %d kernel kinds; step %.3f ms\n" % (sum(r[1] for r in rows), len(rows),
+                                                                                ms_step))
+                for name, ms, cnt in rows[:60]:
+                    fh.write("%8.3f ms x%-6.1f %s\n" % (ms, cnt, name[:160]))
+    if os.environ.get("B200DDP_TRACE", "0") == "1" and hasattr(ddp, "bucket_trace") and rank == 0:
+        print("bucket trace (us): " + json.dumps(ddp.bucket_trace()), file=sys.stderr, flush=True)
 
     # ---- self-check: replicas bit-identical after all the timed steps (vouches for the collectives), loss finite
     replicas_identical = None

@@ -153,7 +153,10 @@ __global__ void __launch_bounds__(kFinThreads)
         total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
       }
     }
-    xgpu_barrier(xg, blockIdx.x);  // nobody overwrites its slot while a peer may still be reading it
+    // No trailing barrier: the caller alternates slot_off between two exchange areas from call to call, and a rank
+    // can only be two calls ahead of a peer after that peer has arrived at the barrier in between, i.e. after the
+    // peer's previous kernel (whose reads of this area are the last ones) has completed. One device barrier per
+    // BatchNorm instead of two (SyncBatchNorm of torch: a blocking all_gather + a host sync per layer).
   }
   if (rg != 0) return;
   const float mean = s / total;
@@ -307,7 +310,7 @@ __global__ void __launch_bounds__(kFinThreads)
         total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
       }
     }
-    xgpu_barrier(xg, blockIdx.x);
+    // (no trailing barrier: alternating exchange areas, see bn_finalize_kernel)
   }
   if (rg != 0) return;
   const float is = invstd[c], mu = mean[c], g = gamma[c];

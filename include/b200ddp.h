@@ -88,7 +88,10 @@ void b2_conv_set_impl(int impl);
  * BatchNorm (+ReLU, +residual add) forward/backward on NHWC bf16, fp32 statistics (csrc/bn.cu).
  * Reference: torchvision BasicBlock/Bottleneck bn/relu/add reached from resnet/main.py:76,121,123
  * (aten::native_batch_norm[_backward], relu_, add_, threshold_backward); with xg->world > 1 the statistics
- * are reduced across GPUs inside the finalize kernel (torch.nn.SyncBatchNorm's all_gather/all_reduce).
+ * are reduced across GPUs inside the finalize kernel (torch.nn.SyncBatchNorm's all_gather/all_reduce): every rank
+ * publishes its sums at float offset xg_slot of its window, ONE device barrier, every rank adds all ranks' sums in
+ * rank order. The exchange area (2*C + C/8 floats) must ALTERNATE between two offsets from one cross-GPU call to the
+ * next (forward and backward calls alike), which is what makes a second, trailing barrier unnecessary.
  * y: conv output [M,C]; z: block output; partial: scratch of b2_bn_partial_floats(C) floats.
  * ---------------------------------------------------------------------------------------------- */
 long long b2_bn_partial_floats(int C);
@@ -153,6 +156,25 @@ int b2_ce_fwd(const void* logits, const long long* labels, float* lse, float* lo
 int b2_ce_bwd(const void* logits, const long long* labels, const float* lse, const float* gscale, void* dlogits,
               float* dbias, int accumulate_bias, int rows, int ncls, int ld, void* stream);
 int b2_colsum_bf16(const void* m, float* out, int rows, int cols, int ld, int accumulate, void* stream);
+/* Fused classifier head (csrc/head.cu). Reference: resnet/main.py:121-122 (`ddp_model(inputs)` ends in
+ * torchvision's avgpool -> flatten -> fc; `criterion(outputs, labels)` is log_softmax + nll_loss).
+ * b2_head_fwd: global average pool of the NHWC bf16 feature map x [N][HW][C] and the fully connected layer in one
+ * kernel (clusters of 8 CTAs share the pooled operand through distributed shared memory, tcgen05 MMA with the
+ * accumulator in TMEM): logits [N][ld] fp32 = mean_hw(x) . w^T + bias, w [ncls][C] bf16; the bf16 pooled matrix
+ * [N][C] is also written out (the weight-gradient GEMM of the backward pass reads it).
+ * b2_head_supported: C a power-of-two multiple of 64 up to 2048, ncls <= 1024.
+ * b2_ce_fwd_f32: per-row log-sum-exp (lse) and the mean NLL loss from fp32 logits, one launch; counter is one
+ * zero-initialised u32 of device scratch (the kernel leaves it zero).
+ * b2_ce_bwd_fused: dlogits (bf16, row stride ld_out) = (softmax - onehot) * (*gscale) / rows and the bias gradient
+ * dbias[ncls] (written, or added to when accumulate_bias) in one launch. */
+int b2_head_supported(int C, int ncls);
+int b2_head_fwd(const void* x, const void* w_bf16, const float* bias, void* pooled, float* logits, int N, int HW,
+                int C, int ncls, int ld, void* stream);
+int b2_ce_fwd_f32(const float* logits, const long long* labels, float* lse, float* loss_row, float* loss,
+                  unsigned int* counter, int rows, int ncls, int ld, void* stream);
+int b2_ce_bwd_fused(const float* logits, const long long* labels, const float* lse, const float* gscale,
+                    void* dlogits_bf16, float* dbias, int accumulate_bias, int rows, int ncls, int ld, int ld_out,
+                    void* stream);
 /* p, g, buf: flat fp32; shadow: optional bf16 copy of p refreshed in the same pass.
  * hyper_dev (nullable): three floats in device memory {lr, momentum, weight_decay} read by the kernel instead of the
  * by-value arguments, so a learning-rate schedule does not change the launch (and a captured CUDA graph stays valid). */

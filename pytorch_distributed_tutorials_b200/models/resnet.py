@@ -218,6 +218,43 @@ class _Rec:
         self.x, self.y, self.mask, self.conv, self.bn, self.relu, self.stem_a = x, y, mask, conv, bn, relu, stem_a
 
 
+class _HeadLink:
+    """Private channel between the engine and ``ops.loss.CrossEntropyLoss``. The model returns fp32 logits and the
+    criterion is a separate call (reference resnet/main.py:121-122), so by autograd's contract the engine would
+    receive an fp32 ``dlogits`` tensor and have to cast it to bf16 for its GEMMs. With this link (attached to the
+    logits tensor as ``_b2_head``) our loss kernel writes bf16 ``dlogits`` and the classifier's bias gradient
+    straight where the engine's backward wants them and returns a zero-stride placeholder to autograd."""
+
+    def __init__(self, engine):
+        self.engine = engine
+        self.ready = False
+        self.logits_ptr = None
+        self.dl = None
+        self.slot = None
+        self._placeholder = None
+
+    def arm(self, logits):
+        self.ready, self.slot, self.dl = False, None, None
+        self.logits_ptr = logits.data_ptr()
+
+    def accepts(self, lg):
+        return lg.data_ptr() == self.logits_ptr and lg.dtype == torch.float32
+
+    def dlogits_buffer(self, shape):
+        n = shape[0] * shape[1]
+        self.dl = native.scratch(self.engine.device, "head_dlogits", n, torch.bfloat16)[:n].view(shape)
+        return self.dl
+
+    def bias_slot(self):
+        self.slot = self.engine._slot(self.engine.model.fc.bias)
+        return self.slot[0], self.slot[1]
+
+    def placeholder(self, shape):
+        if self._placeholder is None:
+            self._placeholder = torch.zeros((), dtype=torch.float32, device=self.engine.device)
+        return self._placeholder.expand(shape)
+
+
 class ResNetEngine:
     """Runs a :class:`ResNet` on the native kernels. One instance per model; holds only scratch state."""
 
@@ -244,6 +281,9 @@ class ResNetEngine:
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
         self.xg_slot = 0           # float offset of the statistics exchange area inside the symmetric window
+        # avgpool + fc as one kernel (csrc/head.cu); B200DDP_HEAD=split selects avgpool kernel + GEMM instead
+        self.fused_head = os.environ.get("B200DDP_HEAD", "fused") != "split"
+        self.head_link = _HeadLink(self)
 
     # ------------------------------------------------------------------ helpers
     def _bn(self, bn):
@@ -274,6 +314,17 @@ class ResNetEngine:
 
     def _sync_bn_ctx(self, bn):
         return self.xg if getattr(bn, "_b2_sync", False) and self.xg is not None else None
+
+    XG_SLOT_FLOATS = 2 * 2048 + 256     # one exchange area: (sum, sumsq | sum_dy, sum_dy_xmu) + per-CTA counts
+
+    def _next_xg_slot(self, bn):
+        """Exchange area of the next cross-GPU BatchNorm call: two areas used alternately, so the kernels need one
+        device barrier per call, not two (csrc/bn.cu). A pure call counter: identical on every rank, and a captured
+        step contains an even number of calls (forward + backward of every BatchNorm), so replays keep alternating."""
+        if self._sync_bn_ctx(bn) is None:
+            return self.xg_slot
+        self._xg_calls = getattr(self, "_xg_calls", 0) + 1
+        return self.xg_slot + (self._xg_calls & 1) * self.XG_SLOT_FLOATS
 
     # ------------------------------------------------------------------ forward units
     def _conv(self, x, conv):
@@ -307,7 +358,7 @@ class ResNetEngine:
             return native.bn_fwd_train(y, res, bn.weight, bn.bias, bn.running_mean if track else None,
                                        bn.running_var if track else None,
                                        bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
-                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self.xg_slot, mask,
+                                       st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self._next_xg_slot(bn), mask,
                                        partial_blocks)
         return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
                                   st.scale_shift)
@@ -367,8 +418,12 @@ class ResNetEngine:
                 cur = self._unit(h, conv, bn, True, idn, training, bt)
                 if tape is not None:
                     block_tapes.append((blk, bt))
-        pooled = native.avgpool_fwd(cur)
-        logits = convops.gemm_nt(pooled, self._w16(m.fc.weight), m.fc.bias.detach())
+        w_fc = self._w16(m.fc.weight)
+        if self.fused_head and native.head_supported(cur.shape[1], w_fc.shape[0]):
+            logits, pooled = native.head_fwd(cur, w_fc, m.fc.bias.detach())     # fp32 logits, no cast afterwards
+        else:
+            pooled = native.avgpool_fwd(cur)
+            logits = convops.gemm_nt(pooled, w_fc, m.fc.bias.detach()).float()
         if tape is not None:
             tape.append(("head", z.shape, pool_idx, block_tapes, cur.shape, pooled))
         return logits
@@ -408,17 +463,17 @@ class ResNetEngine:
             dy = native.bn_bwd_partial(dz_a, rec.y, bn.weight, st.mean, st.invstd, dg_slot[0], db_slot[0],
                                        dg_slot[1] and db_slot[1], rec.relu and not pre_masked, st.coef,
                                        native.bn_partial_b(self.device), given_blocks,
-                                       self._sync_bn_ctx(bn), self.xg_slot, None if pre_masked else rec.mask)
+                                       self._sync_bn_ctx(bn), self._next_xg_slot(bn), None if pre_masked else rec.mask)
             dres = dz_a if pre_masked else None
         elif pre_masked:
             dy, _ = native.bn_bwd(dz_a, None, None, rec.y, bn.weight, st.mean, st.invstd,
                                   dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], False, st.coef, False,
-                                  self._sync_bn_ctx(bn), self.xg_slot, None)
+                                  self._sync_bn_ctx(bn), self._next_xg_slot(bn), None)
             dres = dz_a
         else:
             dy, dres = native.bn_bwd(dz_a, dz_b, None, rec.y, bn.weight, st.mean, st.invstd,
                                      dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
-                                     self._sync_bn_ctx(bn), self.xg_slot, rec.mask)
+                                     self._sync_bn_ctx(bn), self._next_xg_slot(bn), rec.mask)
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight
@@ -475,11 +530,20 @@ class ResNetEngine:
         grads = {}
         head = tape[-1]
         _, stem_shape, pool_idx, block_tapes, feat_shape, pooled = head
-        dl = dlogits if dlogits.dtype == torch.bfloat16 else dlogits.to(torch.bfloat16)
-        dl = dl.contiguous()
+        link = self.head_link
+        if link.ready:
+            # our criterion already left bf16 dlogits and the bias gradient in place (dlogits is a placeholder)
+            dl, bias_slot = link.dl, link.slot
+            link.ready = False
+        else:
+            dl = dlogits if dlogits.dtype == torch.bfloat16 else dlogits.to(torch.bfloat16)
+            dl, bias_slot = dl.contiguous(), None
         # classifier: bias grad (column sum), weight grad (dl^T @ pooled), input grad (dl @ W)
         dpooled = convops.gemm_nn(dl, self._w16(m.fc.weight))   # before the fc gradients are delivered (see _unit_bwd)
-        grads[id(m.fc.bias)] = self._deliver(m.fc.bias, lambda out, acc: native.colsum_bf16(dl, out, acc))
+        if bias_slot is not None:
+            self._publish(m.fc.bias, bias_slot, grads)
+        else:
+            grads[id(m.fc.bias)] = self._deliver(m.fc.bias, lambda out, acc: native.colsum_bf16(dl, out, acc))
         grads[id(m.fc.weight)] = self._deliver(m.fc.weight, lambda out, acc: convops.gemm_tn(dl, pooled, out, acc))
         da, db = native.avgpool_bwd(dpooled, feat_shape), None
         rev = list(reversed(block_tapes))
@@ -531,8 +595,11 @@ class ResNetEngine:
     def _call(self, x, training):
         m = self.model
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.params):
-            return _EngineFn.apply(self, x, training, *self.params)
-        return self._run_forward(x, training, None).float()
+            out = _EngineFn.apply(self, x, training, *self.params)
+            self.head_link.arm(out)
+            out._b2_head = self.head_link
+            return out
+        return self._run_forward(x, training, None)
 
 
 class _EngineFn(torch.autograd.Function):
@@ -543,7 +610,7 @@ class _EngineFn(torch.autograd.Function):
         ctx.engine = engine
         ctx.tape = tape
         ctx.nparams = len(params)
-        return logits.float()
+        return logits
 
     @staticmethod
     def backward(ctx, dlogits):

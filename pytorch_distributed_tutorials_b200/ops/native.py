@@ -174,6 +174,60 @@ def ce_bwd(logits, labels, lse, gscale, dbias=None, accumulate_bias=False):
     return dlogits
 
 
+# ------------------------------------------------------------------------------------------------ fused head
+def head_supported(c, ncls):
+    return bool(_lib.lib().b2_head_supported(int(c), int(ncls)))
+
+
+def head_fwd(x, w16, bias):
+    """aten::mean (global average pool) + addmm (fc) in one kernel (csrc/head.cu): x [N,C,H,W] channels_last bf16,
+    w16 [ncls,C] bf16, bias fp32 -> (logits [N,ncls] fp32, pooled [N,C] bf16 kept for the backward pass)."""
+    n, c, h, w = x.shape
+    ncls = w16.shape[0]
+    logits = torch.empty((n, ncls), dtype=torch.float32, device=x.device)
+    pooled = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().b2_head_fwd(ptr(x), ptr(w16), ptr(bias), ptr(pooled), ptr(logits), n, h * w, c, ncls, ncls,
+                                 stream_ptr()), "b2_head_fwd")
+    count_launch()
+    return logits, pooled
+
+
+_zero_scratch = {}
+
+
+def zero_scratch(device, key, numel, dtype):
+    """Persistent scratch that starts zeroed (and that its kernels leave zeroed)."""
+    k = (device, key)
+    t = _zero_scratch.get(k)
+    if t is None or t.numel() < numel:
+        t = _zero_scratch[k] = torch.zeros(numel, dtype=dtype, device=device)
+    return t
+
+
+def ce_fwd_f32(logits, labels):
+    """aten::_log_softmax + nll_loss_forward (mean) on fp32 logits, one launch. Returns (loss scalar, lse)."""
+    rows, ncls = logits.shape
+    lse = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    loss_row = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    counter = zero_scratch(logits.device, "ce_counter", 1, torch.int32)
+    check(_lib.lib().b2_ce_fwd_f32(ptr(logits), ptr(labels), ptr(lse), ptr(loss_row), ptr(loss), ptr(counter), rows,
+                                   ncls, logits.stride(0), stream_ptr()), "b2_ce_fwd_f32")
+    count_launch()
+    return loss, lse
+
+
+def ce_bwd_fused(logits, labels, lse, gscale, dlogits16, dbias=None, accumulate_bias=False):
+    """_log_softmax_backward + nll_loss_backward: bf16 dlogits and (optionally) the classifier's bias gradient in
+    one launch."""
+    rows, ncls = logits.shape
+    check(_lib.lib().b2_ce_bwd_fused(ptr(logits), ptr(labels), ptr(lse), ptr(gscale), ptr(dlogits16), ptr(dbias),
+                                     int(accumulate_bias), rows, ncls, logits.stride(0), dlogits16.stride(0),
+                                     stream_ptr()), "b2_ce_bwd_fused")
+    count_launch()
+    return dlogits16
+
+
 def colsum_bf16(m, out, accumulate=False):
     rows, cols = m.shape
     check(_lib.lib().b2_colsum_bf16(ptr(m), ptr(out), rows, cols, m.stride(0), int(accumulate), stream_ptr()),

@@ -136,9 +136,15 @@ class DistributedDataParallel(nn.Module):
         # exposed-tail cut (P2P backend only; the CPU / torch back ends keep torch's exact bucket tables)
         tail = self._tail_bucket_mb
         if tail is None:
-            tail = float(os.environ.get("B200DDP_TAIL_BUCKET_MB", "1" if backend == "p2p" else "0"))
-        if tail > 0 and self.world > 1:
-            self.bucket_of_param = split_tail_bucket(self.bucket_of_param, sizes, int(tail * MiB))
+            tail = os.environ.get("B200DDP_TAIL_BUCKET_MB", "1,0.0625" if backend == "p2p" else "0")
+        tails = [float(t) for t in str(tail).split(",")] if not isinstance(tail, (int, float)) else [float(tail)]
+        if self.world > 1:
+            # successive cuts (1 MiB, then 64 KiB by default): what is left exposed after backward's last kernel is
+            # one latency-bound one-shot reduction of the stem's gradients; the 1 MiB before it hides behind the
+            # stem's own backward kernels
+            for t in tails:
+                if t > 0:
+                    self.bucket_of_param = split_tail_bucket(self.bucket_of_param, sizes, int(t * MiB))
         if backend == "p2p":
             total = sum((p.numel() + 63) // 64 * 64 for p in ordered) * 4
             buf_bytes = sum((b.numel() * b.element_size() + 255) // 256 * 256 for b in buffers)
@@ -284,7 +290,7 @@ class DistributedDataParallel(nn.Module):
             slot = 0
             if self.backend == "p2p":
                 # exchange area for per-GPU BN statistics: (sum, sumsq | sum_dy, sum_dy_xmu) + per-CTA counts
-                slot = self.comm.window.alloc(4 * (2 * 2048 + 256)) // 4
+                slot = self.comm.window.alloc(2 * 4 * (2 * 2048 + 256)) // 4   # two areas, used alternately
             self.module._b2_xgpu_slot = slot
             if eng is not None:
                 eng.xg = self.xgpu_compute_ctx

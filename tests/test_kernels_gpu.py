@@ -153,6 +153,53 @@ def test_avgpool():
     assert _rel(dx, (dy.float() / 49)[:, :, None, None].expand(5, 2048, 7, 7)) < 1e-2
 
 
+@pytest.mark.parametrize("N,C,HW,ncls", [(256, 2048, 49, 1000), (37, 2048, 49, 1000), (16, 512, 1, 1000),
+                                          (5, 512, 4, 10), (40, 1024, 16, 1000), (3, 64, 9, 24)])
+def test_fused_head_avgpool_fc(N, C, HW, ncls):
+    """avgpool -> fc in one kernel (cluster DSMEM pooled operand, tcgen05) against fp32 torch: logits fp32, pooled
+    bf16. The oracle pools in fp32, rounds the mean to bf16 (as the kernel does, and as a bf16 avgpool would) and
+    multiplies in fp32."""
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(N + C)
+    side = int(HW ** 0.5)
+    assert side * side == HW
+    x = _bf(torch.randn(N, C, side, side, device=DEV) + 0.5)
+    w = (torch.randn(ncls, C, device=DEV) / C ** 0.5).to(torch.bfloat16)
+    b = torch.randn(ncls, device=DEV)
+    assert native.head_supported(C, ncls)
+    logits, pooled = native.head_fwd(x, w, b)
+    torch.cuda.synchronize()
+    pm = x.float().mean((2, 3))
+    assert torch.isfinite(logits).all()
+    assert _rel(pooled, pm) < 5e-3
+    ref = pm.to(torch.bfloat16).float() @ w.float().t() + b
+    assert _rel(logits, ref) < 2e-3, _rel(logits, ref)
+
+
+def test_cross_entropy_backward_emits_bias_gradient():
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(9)
+    for rows, ncls in ((256, 1000), (33, 1000), (7, 10)):
+        logits = torch.randn(rows, ncls, device=DEV) * 3
+        labels = torch.randint(0, ncls, (rows,), device=DEV)
+        loss, lse = native.ce_fwd_f32(logits, labels)
+        ref = logits.clone().requires_grad_(True)
+        lr = F.cross_entropy(ref, labels)
+        lr.backward()
+        assert abs(loss.item() - lr.item()) < 1e-4 * max(1.0, abs(lr.item()))
+        assert torch.allclose(lse, torch.logsumexp(logits, 1), atol=1e-4)
+        g = torch.tensor(2.0, device=DEV)
+        dl = torch.full((rows, ncls), float("nan"), device=DEV, dtype=torch.bfloat16)
+        db = torch.full((ncls,), float("nan"), device=DEV)
+        native.ce_bwd_fused(logits, labels, lse, g, dl, db, False)
+        assert _rel(dl, 2.0 * ref.grad) < 1e-2
+        assert torch.allclose(db, dl.float().sum(0), atol=1e-6, rtol=1e-5)
+        native.ce_bwd_fused(logits, labels, lse, g, dl, db, True)
+        assert torch.allclose(db, 2 * dl.float().sum(0), atol=1e-6, rtol=1e-5)
+        loss2, _ = native.ce_fwd_f32(logits, labels)           # the completion counter reset itself
+        assert loss2.item() == loss.item()
+
+
 def test_cross_entropy():
     from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
     torch.manual_seed(4)

@@ -218,9 +218,12 @@ def test_ddp_p2p_trains_like_torch_ddp(world, sync_bn):
     for r in out:
         assert r["backend"] == "p2p"
         assert r["ident"], "replicas drifted apart"
-        # torch's three ResNet-18 buckets, the last one cut once more so that only <= 1 MiB waits for the end of backward
-        assert r["buckets"][:2] == [513000, 7213056] and len(r["buckets"]) == 4 and r["buckets"][3] * 4 <= 1 << 20, r
-        assert r["n_allreduce"] == 5 * 4
+        # torch's bucketing rule in the engine's gradient-ready order, the last bucket cut twice more so that only
+        # the stem's gradients (<= 64 KiB) wait for the very end of backward
+        bk = r["buckets"]
+        assert bk[0] == 513000 and sum(bk) == 11689512 and len(bk) == 5 and bk[-1] * 4 <= 64 << 10 \
+            and bk[-2] * 4 <= 1 << 20, bk
+        assert r["n_allreduce"] == 5 * len(bk)
         assert r["exposed"] is not None and r["exposed"] >= 0.0
         assert r["ours"][-1] < r["ours"][0]
         assert abs(r["ours"][0] - r["theirs"][0]) < 0.05 * r["theirs"][0], r
@@ -235,7 +238,13 @@ def _syncbn_stats(rank, world):
     dev = torch.device("cuda", rank)
     comm = P2PComm(dev, None, 64 << 20)
     xg = comm.window.ctx(P2PComm.PAD_COMPUTE)
-    slot = comm.window.alloc(4 * (2 * 2048 + 256)) // 4
+    area = 2 * 2048 + 256
+    slot0 = comm.window.alloc(2 * 4 * area) // 4     # two exchange areas, alternated call by call (one barrier each)
+    calls = [0]
+
+    def next_slot():
+        calls[0] += 1
+        return slot0 + (calls[0] & 1) * area
     out = {}
     for C, H, N in [(64, 9, 3 + rank), (512, 5, 2), (2048, 3, 4)]:
         torch.manual_seed(100 + rank)
@@ -247,7 +256,7 @@ def _syncbn_stats(rank, world):
         rm, rv, nbt = torch.zeros(C, device=dev), torch.ones(C, device=dev), torch.tensor(0, device=dev)
         mean, invstd = torch.empty(C, device=dev), torch.empty(C, device=dev)
         ss, coef = torch.empty(2 * C, device=dev), torch.empty(3 * C, device=dev)
-        z = native.bn_fwd_train(y, None, gamma, beta, rm, rv, nbt, 0.1, 1e-5, True, mean, invstd, ss, xg, slot)
+        z = native.bn_fwd_train(y, None, gamma, beta, rm, rv, nbt, 0.1, 1e-5, True, mean, invstd, ss, xg, next_slot())
         ref = nn.SyncBatchNorm(C).to(dev)
         with torch.no_grad():
             ref.weight.copy_(gamma)
@@ -259,7 +268,7 @@ def _syncbn_stats(rank, world):
         out["rv_%d" % C] = ((rv - ref.running_var).abs().max() / ref.running_var.abs().max()).item()
         dz = torch.randn_like(zr).to(torch.bfloat16)
         dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
-        dy, _ = native.bn_bwd(dz, None, z, y, gamma, mean, invstd, dg, db, False, True, coef, False, xg, slot)
+        dy, _ = native.bn_bwd(dz, None, z, y, gamma, mean, invstd, dg, db, False, True, coef, False, xg, next_slot())
         zr.backward(dz.float() * (z.float() > 0) / 1.0)
         out["bwd_%d" % C] = ((dy.float() - yf.grad).abs().max() / yf.grad.abs().max()).item()
         out["dg_%d" % C] = ((dg - ref.weight.grad).abs().max() / ref.weight.grad.abs().max()).item()

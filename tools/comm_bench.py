@@ -30,16 +30,28 @@ def timed(fn, iters, world):
         fn()
     e1.record()
     e1.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda", dtype=torch.float64)
+    t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)     # CPU tensor: gloo control plane
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
 
 def main():
     lr = int(os.environ.get("LOCAL_RANK", "0"))
-    init_process_group(backend="b200", local_rank=lr)
+    init_process_group(backend="b200", local_rank=lr)   # gloo control plane; the product path creates no NCCL
     rank, world = dist.get_rank(), dist.get_world_size()
     dev = torch.device("cuda", lr)
+    # the baselines get their own NCCL group: dist.all_reduce over it, and torch's symmetric-memory all-reduces
+    # (one_shot_all_reduce / two_shot_all_reduce_ / multimem_all_reduce_, "the kernels to beat")
+    nccl = dist.new_group(backend="nccl", device_id=dev)
+    symm, symm_err = None, None
+    try:
+        import torch.distributed._symmetric_memory as symm
+        try:
+            symm.enable_symm_mem_for_group(nccl.group_name)
+        except Exception:  # noqa: BLE001  (deprecated / implicit in newer torch)
+            pass
+    except Exception as e:  # noqa: BLE001
+        symm, symm_err = None, repr(e)
     comm = P2PComm(dev, None, 1200 << 20)
     if rank == 0:
         print(json.dumps({"world": world, "transport": comm.window.transport, "multicast": bool(comm.mc_base),
@@ -57,7 +69,29 @@ def main():
         ref = torch.randn(n, device=dev)
         iters = 50 if n < (1 << 22) else 15
         row = {"name": name, "bytes": n * 4}
-        row["nccl_us"] = 1e3 * timed(lambda: dist.all_reduce(ref), iters, world)
+        row["nccl_us"] = 1e3 * timed(lambda: dist.all_reduce(ref, group=nccl), iters, world)
+        if symm is not None:
+            try:
+                st = symm.empty(n, dtype=torch.float32, device=dev)
+                symm.rendezvous(st, nccl.group_name)
+                st.normal_()
+                gname = nccl.group_name
+                if n * 4 <= (8 << 20):
+                    row["torch_symm_one_shot_us"] = 1e3 * timed(
+                        lambda: torch.ops.symm_mem.one_shot_all_reduce(st, "sum", gname), iters, world)
+                row["torch_symm_two_shot_us"] = 1e3 * timed(
+                    lambda: torch.ops.symm_mem.two_shot_all_reduce_(st, "sum", gname), iters, world)
+                try:
+                    row["torch_symm_multimem_us"] = 1e3 * timed(
+                        lambda: torch.ops.symm_mem.multimem_all_reduce_(st, "sum", gname), iters, world)
+                except Exception as e:  # noqa: BLE001
+                    row["torch_symm_multimem_err"] = repr(e)[:120]
+                del st
+            except Exception as e:  # noqa: BLE001
+                row["torch_symm_err"] = repr(e)[:160]
+                symm = None
+        elif symm_err:
+            row["torch_symm_err"] = symm_err[:160]
         for algo in ["oneshot", "twoshot"] + (["multimem"] if comm.mc_base else []):
             if algo == "oneshot" and n > 524288:
                 continue
@@ -75,7 +109,7 @@ def main():
         opt = torch.optim.SGD([p], lr=0.01, momentum=0.9, weight_decay=1e-5, fused=True)
         def unfused():
             p.grad.div_(world)
-            dist.all_reduce(p.grad)
+            dist.all_reduce(p.grad, group=nccl)
             opt.step()
         row["nccl_plus_fused_sgd_us"] = 1e3 * timed(unfused, iters, world)
         k = 2.0 * (world - 1) / world * n * 4
