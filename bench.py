@@ -330,6 +330,7 @@ def main():
         launches = _lib.launches()
         exposed = ddp.exposed_comm_ms(last=args.steps) if (args.impl == "ours" and hasattr(ddp, "exposed_comm_ms")) \
             else None
+        anatomy = ddp.step_anatomy(last=args.steps) if (args.impl == "ours" and hasattr(ddp, "step_anatomy")) else None
         if len(clocks.rows) < 2:                    # very short runs: keep the load on until two samples exist
             t_wait = time.monotonic()
             while len(clocks.rows) < 2 and time.monotonic() - t_wait < 3.0:
@@ -431,6 +432,7 @@ def main():
                                  "end of backward compute" if args.impl == "ours" else
                                  "backward(sync) - backward(no_sync), CUDA events"),
             "comm_overhead_bwd_ms": overhead,
+            "step_anatomy_ms": anatomy,
             "replicas_identical": replicas_identical,
         }
         if args.impl == "reference":

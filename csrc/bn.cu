@@ -278,6 +278,90 @@ __global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
   }
 }
 
+// Same pass with the loads of U row groups issued back to back before any of them is consumed (explicit software
+// batching: U * (2..3) independent 16-byte loads + U mask bytes in flight per thread). The plain loop above leaves it
+// to the compiler to hoist loads across the unrolled iterations, which the 64-register cap of 4 CTAs/SM prevents:
+// ncu showed the kernel waiting on long_scoreboard at 49 % occupancy and 75 % of the measured HBM peak.
+// BPS = CTAs per SM the register budget is sized for (fewer CTAs, more registers, more loads in flight each).
+template <bool RELU, bool TWO, bool GOUT, int U, int BPS>
+__global__ void __launch_bounds__(kBnThreads, BPS)
+    bn_bwd_reduce_batched_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
+                                 const unsigned char* __restrict__ mask, const __nv_bfloat16* __restrict__ y,
+                                 const float* __restrict__ mean, float* partial, __nv_bfloat16* __restrict__ gout,
+                                 long long M, int C) {
+  extern __shared__ float smem[];
+  const int C8 = C >> 3, RP = kBnThreads / C8;
+  const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+  if (r < RP) {
+    const Vec8 mu = load_f32x8(mean + cv * 8);
+    const long long step = (long long)gridDim.x * RP;
+    for (long long row0 = (long long)blockIdx.x * RP + r; row0 < M; row0 += step * U) {
+      uint4 ua[U], ub[U], uy[U];
+      unsigned bits[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long row = row0 + u * step;
+        if (row < M) {
+          const long long off = row * C + cv * 8;
+          ua[u] = ld_nc_v4(dza + off);
+          if (TWO) ub[u] = ld_nc_v4(dzb + off);
+          uy[u] = ld_nc_v4(y + off);
+          if (RELU) bits[u] = mask[off >> 3];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long row = row0 + u * step;
+        if (row < M) {
+          const long long off = row * C + cv * 8;
+          float g[8], yy[8];
+          {
+            const float2 a0 = unpack_bf16x2(ua[u].x), a1 = unpack_bf16x2(ua[u].y), a2 = unpack_bf16x2(ua[u].z),
+                         a3 = unpack_bf16x2(ua[u].w);
+            g[0] = a0.x; g[1] = a0.y; g[2] = a1.x; g[3] = a1.y; g[4] = a2.x; g[5] = a2.y; g[6] = a3.x; g[7] = a3.y;
+          }
+          if (TWO) {
+            const float2 a0 = unpack_bf16x2(ub[u].x), a1 = unpack_bf16x2(ub[u].y), a2 = unpack_bf16x2(ub[u].z),
+                         a3 = unpack_bf16x2(ub[u].w);
+            g[0] += a0.x; g[1] += a0.y; g[2] += a1.x; g[3] += a1.y; g[4] += a2.x; g[5] += a2.y; g[6] += a3.x;
+            g[7] += a3.y;
+          }
+          if (RELU) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[j] = ((bits[u] >> j) & 1u) ? g[j] : 0.f;
+          }
+          if (GOUT) {
+            uint4 o;
+            o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]);
+            o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
+            *reinterpret_cast<uint4*>(gout + off) = o;
+            const float2 a0 = unpack_bf16x2(o.x), a1 = unpack_bf16x2(o.y), a2 = unpack_bf16x2(o.z),
+                         a3 = unpack_bf16x2(o.w);   // the sums use the rounded values, as the apply pass will
+            g[0] = a0.x; g[1] = a0.y; g[2] = a1.x; g[3] = a1.y; g[4] = a2.x; g[5] = a2.y; g[6] = a3.x; g[7] = a3.y;
+          }
+          {
+            const float2 a0 = unpack_bf16x2(uy[u].x), a1 = unpack_bf16x2(uy[u].y), a2 = unpack_bf16x2(uy[u].z),
+                         a3 = unpack_bf16x2(uy[u].w);
+            yy[0] = a0.x; yy[1] = a0.y; yy[2] = a1.x; yy[3] = a1.y; yy[4] = a2.x; yy[5] = a2.y; yy[6] = a3.x;
+            yy[7] = a3.y;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            acc[0][j] += g[j];
+            acc[1][j] += g[j] * (yy[j] - mu.v[j]);
+          }
+        }
+      }
+    }
+    block_reduce_store<2>(acc, smem, partial, C, C8, RP, cv, r, C);
+  } else {
+    __syncthreads();
+  }
+}
+
 // partials -> dgamma/dbeta (fp32, optionally accumulated into existing grads) and the three per-channel
 // coefficients of  dy = k1*dz' + k2*y + k3.  With world > 1 the two sums are reduced across GPUs in-kernel.
 __global__ void __launch_bounds__(kFinThreads)
@@ -363,6 +447,11 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// 0 = plain loop, 1 = batched loads x2 @ 4 CTAs/SM, 2 = x4 @ 2 CTAs/SM, 3 = x3 @ 3 CTAs/SM (b2_bn_set_reduce_variant)
+// Default 2: measured on B200 (tools/bn_bench.py, batch 256, reduce + apply of a residual block output):
+// C=256 @56x56 0.546 ms (variant 0) / 0.535 (1) / 0.475 (2) / 0.497 (3); every ResNet-50 shape ranks the same way.
+static int g_bn_reduce_variant = 2;
+
 static int plan_blocks(long long M, int C, long long* rows_per_blk) {
   const int C8 = C / 8, RP = kBnThreads / C8;
   long long nblk = (M + (long long)RP * 8 - 1) / ((long long)RP * 8);
@@ -389,6 +478,7 @@ using namespace b2;
 
 B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_bn)
 
+extern "C" void b2_bn_set_reduce_variant(int v) { g_bn_reduce_variant = (v >= 0 && v <= 3) ? v : 0; }
 extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartialBlocks * 2 * C; }
 
 static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }
@@ -520,10 +610,34 @@ static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const 
     if (dres) bn_bwd_reduce_kernel<R, T, true><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb); \
     else bn_bwd_reduce_kernel<R, T, false><<<nblk, kBnThreads, sm, st>>>(a, b, zz, mk, yy, mean, partial, drp, M, C, rpb);     \
   } while (0)
-  if (given_blocks > 0)
+#define REDB(R, T, UU, BPS)                                                                                         \
+  do {                                                                                                              \
+    if (dres) bn_bwd_reduce_batched_kernel<R, T, true, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C); \
+    else bn_bwd_reduce_batched_kernel<R, T, false, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C);     \
+  } while (0)
+#define REDV(UU, BPS)                                        \
+  do {                                                       \
+    if (relu && dzb) REDB(true, true, UU, BPS);              \
+    else if (relu) REDB(true, false, UU, BPS);               \
+    else if (dzb) REDB(false, true, UU, BPS);                \
+    else REDB(false, false, UU, BPS);                        \
+  } while (0)
+  // batched variants need the 1-bit ReLU mask (or no ReLU); the z-tensor form keeps the plain loop
+  const int variant = (relu && !mk) ? 0 : g_bn_reduce_variant;
+  if (given_blocks > 0) {
     nblk = given_blocks;
-  else
+  } else if (variant == 0) {
     B2_BWD_DISPATCH(RED, 0);
+  } else {
+    const int bps = variant == 1 ? 4 : (variant == 2 ? 2 : 3);
+    long long cap = (long long)host_num_sms() * bps;
+    if (nblk > cap) nblk = (int)cap;
+    if (variant == 1) REDV(2, 4);
+    else if (variant == 2) REDV(4, 2);
+    else REDV(3, 3);
+  }
+#undef REDV
+#undef REDB
 #undef RED
   XgpuCtx ctx = xgpu_from_c(xg);
   bn_bwd_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(partial, nblk, C, (float)M, gamma, mean, invstd, dgamma,

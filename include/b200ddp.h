@@ -95,6 +95,9 @@ void b2_conv_set_impl(int impl);
  * y: conv output [M,C]; z: block output; partial: scratch of b2_bn_partial_floats(C) floats.
  * ---------------------------------------------------------------------------------------------- */
 long long b2_bn_partial_floats(int C);
+/* Tuning: load batching of the backward reduce pass. 0 = plain unrolled loop, 1 = 2 row groups of loads issued back
+ * to back @ 4 CTAs/SM, 2 = 4 groups @ 2 CTAs/SM, 3 = 3 groups @ 3 CTAs/SM. */
+void b2_bn_set_reduce_variant(int v);
 /* relu_mask (optional, u8 [M*C/8]): one bit per output element, set where the ReLU passed; the backward pass can
  * then be given the mask instead of z (16x fewer bytes). */
 int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,

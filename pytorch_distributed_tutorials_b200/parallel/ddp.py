@@ -70,12 +70,13 @@ def split_tail_bucket(bucket_of_param, sizes_bytes, tail_bytes):
 
 
 def _ready_order(module, params):
+    """(parameters in the order their gradients become ready, whether that order is known statically)."""
     if hasattr(module, "grad_ready_order"):
         order = [p for p in module.grad_ready_order() if p.requires_grad]
         ids = {id(p) for p in order}
         if len(order) == len(params) and ids == {id(p) for p in params}:
-            return order
-    return list(reversed(params))
+            return order, True
+    return list(reversed(params)), False
 
 
 class DistributedDataParallel(nn.Module):
@@ -104,7 +105,7 @@ class DistributedDataParallel(nn.Module):
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
 
         # ---- bucket plan (gradient-ready order; torch's 1 MiB first bucket only with the default cap)
-        ordered = _ready_order(module, params)
+        ordered, self._static_order = _ready_order(module, params)
         if bucket_cap_mb is None:
             first_cap, cap = 1 * MiB, 25 * MiB
         else:
@@ -112,6 +113,7 @@ class DistributedDataParallel(nn.Module):
         sizes = [p.numel() * p.element_size() for p in ordered]
         self.bucket_of_param = plan_buckets(sizes, first_cap, cap)
         self.bucket_cap_bytes = cap
+        self._first_cap_bytes = first_cap
         self._tail_bucket_mb = tail_bucket_mb
 
         # ---- K1: every rank must hold the same parameter shapes
@@ -138,6 +140,7 @@ class DistributedDataParallel(nn.Module):
         if tail is None:
             tail = os.environ.get("B200DDP_TAIL_BUCKET_MB", "1,0.0625" if backend == "p2p" else "0")
         tails = [float(t) for t in str(tail).split(",")] if not isinstance(tail, (int, float)) else [float(tail)]
+        self._tails = tails
         if self.world > 1:
             # successive cuts (1 MiB, then 64 KiB by default): what is left exposed after backward's last kernel is
             # one latency-bound one-shot reduction of the stem's gradients; the 1 MiB before it hides behind the
@@ -152,6 +155,8 @@ class DistributedDataParallel(nn.Module):
             wire = (gradient_wire or os.environ.get("B200DDP_WIRE", "fp32")).lower()
             if wire == "bf16":
                 extra += total // 2 + MiB          # bf16 staging copy of every bucket
+            if not self._static_order:
+                extra += total + MiB               # room for the one-off bucket rebuild in observed ready order
             self.comm = P2PComm(self.device, process_group, total + extra, algo=comm_algo, wire=wire)
         elif backend == "local":
             self.comm = LocalComm(process_group)
@@ -164,7 +169,22 @@ class DistributedDataParallel(nn.Module):
         # ---- flat storage; gradients are bucket views from now on
         self.store = FlatParameterStore(ordered, self.bucket_of_param, self.device,
                                         grad_alloc=self.comm.grad_alloc if backend == "p2p" else None)
-        self.store.on_ready = self._on_param_ready
+        # weak back-references only: the store, the parameters and their autograd hooks must not keep the wrapper
+        # alive, so that dropping the last reference to it releases its peer-memory window (see __del__ / close)
+        wself = weakref.ref(self)
+
+        def _ready(p, _w=wself):
+            d = _w()
+            if d is not None:
+                d._on_param_ready(p)
+
+        def _hook(p, _w=wself):
+            d = _w()
+            if d is not None:
+                d._autograd_hook(p)
+
+        self._weak_ready, self._weak_hook = _ready, _hook
+        self.store.on_ready = _ready
         self._param_index = {id(p): i for i, p in enumerate(ordered)}
         self.ordered_params = ordered
 
@@ -178,11 +198,15 @@ class DistributedDataParallel(nn.Module):
             self._sync_module_states()
 
         L = _lib.lib()
-        arr = (ctypes.c_int * len(ordered))(*self.bucket_of_param)
-        L.b2_reducer_create.restype = ctypes.c_void_p
-        self._reducer = ctypes.c_void_p(L.b2_reducer_create(len(ordered), arr, len(self.store.buckets)))
-        self._launch_buf = (ctypes.c_int * max(1, len(self.store.buckets)))()
-        self._finalizer = weakref.finalize(self, L.b2_reducer_destroy, self._reducer)
+        self._reducer = None
+        self._make_reducer()
+        # K5: a module without a statically known gradient-ready order starts from reversed registration order; the
+        # order observed in the first synchronised backward (rank 0's, broadcast over the control plane) then
+        # replaces it once, before the second training forward - as c10d's Reducer::rebuild_buckets does
+        self._rebuild_pending = (not self._static_order) and self.world > 1 and \
+            os.environ.get("B200DDP_REBUILD_BUCKETS", "1") == "1"
+        self._observed_order = None
+        self.rebuilt_buckets = False
         self._callback_queued = False
         self._fused_args = None
         self._in_backward_iteration = False
@@ -194,16 +218,17 @@ class DistributedDataParallel(nn.Module):
         # end of backward and on the communication stream after the last reduction. Marker kernels are part of a
         # captured graph like any other launch, so exposed communication is measured in steady-state replays too.
         self._ts_cap = 256
-        self._ts_compute = self._ts_comm = None
-        if self.measure_exposed and backend == "p2p":
+        self._ts_compute = self._ts_comm = self._ts_start = None
+        if self.measure_exposed and self.device.type == "cuda" and backend in ("p2p", "local") and _lib.use_native():
             self._ts_compute = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
             self._ts_comm = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
+            self._ts_start = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
         self.trace_buckets = os.environ.get("B200DDP_TRACE", "0") == "1" and backend == "p2p"
         self._bucket_rings = {}
         self._buffers_in_sync = bool(init_sync) or self.world == 1   # constructor broadcast done; False after load_state_dict
         self._post_forward_sync = backend == "p2p" and os.environ.get("B200DDP_BUFFER_SYNC", "post") == "post"
         self._buffer_sync_pending = False
-        self._hooks = [p.register_post_accumulate_grad_hook(self._autograd_hook) for p in ordered]
+        self._hooks = [p.register_post_accumulate_grad_hook(self._weak_hook) for p in ordered]
         self.iterations = 0
         self.xgpu_compute_ctx = self.comm.window.ctx(P2PComm.PAD_COMPUTE) if backend == "p2p" else None
         self._install_syncbn_ctx()
@@ -216,6 +241,52 @@ class DistributedDataParallel(nn.Module):
             self._watchdog = True
         else:
             self._watchdog = False
+
+    # ------------------------------------------------------------------ reducer / bucket rebuild
+    def _make_reducer(self):
+        L = _lib.lib()
+        if self._reducer is not None:
+            self._finalizer.detach()
+            L.b2_reducer_destroy(self._reducer)
+        n = len(self.ordered_params)
+        arr = (ctypes.c_int * n)(*self.bucket_of_param)
+        L.b2_reducer_create.restype = ctypes.c_void_p
+        self._reducer = ctypes.c_void_p(L.b2_reducer_create(n, arr, len(self.store.buckets)))
+        self._launch_buf = (ctypes.c_int * max(1, len(self.store.buckets)))()
+        self._finalizer = weakref.finalize(self, L.b2_reducer_destroy, self._reducer)
+
+    def _record_ready_order(self):
+        """After the first synchronised backward: the order in which the gradients actually arrived."""
+        n = len(self.ordered_params)
+        out = (ctypes.c_int * n)()
+        got = _lib.lib().b2_reducer_ready_order(self._reducer, out)
+        if got == n:
+            self._observed_order = list(out)
+
+    def _rebuild_buckets(self):
+        """K5 (``Reducer::rebuild_buckets`` + ``sync_bucket_indices`` of the reference stack): re-plan the buckets
+        in rank 0's observed gradient-ready order so that reductions of a generic module overlap its backward."""
+        self._rebuild_pending = False
+        order = [self._observed_order]
+        dist.broadcast_object_list(order, src=0, group=self.process_group)      # every rank adopts rank 0's order
+        order = order[0]
+        self.comm.launch_log.append(("broadcast_order", len(order)))
+        if order is None or order == list(range(len(order))):
+            return
+        params = [self.ordered_params[i] for i in order]
+        sizes = [p.numel() * p.element_size() for p in params]
+        plan = plan_buckets(sizes, self._first_cap_bytes, self.bucket_cap_bytes)
+        for t in self._tails:
+            if t > 0:
+                plan = split_tail_bucket(plan, sizes, int(t * MiB))
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self.store.rebuild(params, plan, grad_alloc=self.comm.grad_alloc if self.backend == "p2p" else None)
+        self.ordered_params = params
+        self.bucket_of_param = plan
+        self._param_index = {id(p): i for i, p in enumerate(params)}
+        self._make_reducer()
+        self.rebuilt_buckets = True
 
     # ------------------------------------------------------------------ buffers
     def _setup_buffers(self, buffers):
@@ -313,7 +384,13 @@ class DistributedDataParallel(nn.Module):
         grad_mode = torch.is_grad_enabled()
         training_fwd = grad_mode and self.module.training
         if training_fwd:
+            if self._ts_start is not None and self.require_backward_grad_sync:
+                _lib.lib().b2_timestamp(ctypes.c_void_p(self._ts_start.data_ptr()), self._ts_cap, ctypes.c_void_p(
+                    torch.cuda.current_stream(self.device).cuda_stream))
+                _lib.count_launch()
             if self.require_backward_grad_sync:
+                if self._rebuild_pending and self._observed_order is not None:
+                    self._rebuild_buckets()
                 _lib.lib().b2_reducer_reset(self._reducer)
                 self._callback_queued = False
                 self._fused_args = None
@@ -401,13 +478,16 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._in_backward_iteration = False
         left = _lib.lib().b2_reducer_unlaunched(self._reducer)
+        if self._rebuild_pending and self._observed_order is None and not left:
+            self._record_ready_order()
         if self._ts_compute is not None:
             # exposed communication = how long the reductions outlast backward's own kernels (device clock)
             L = _lib.lib()
             L.b2_timestamp(ctypes.c_void_p(self._ts_compute.data_ptr()), self._ts_cap,
                            ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+            comm_stream = getattr(self.comm, "stream", None) or torch.cuda.current_stream(self.device)
             L.b2_timestamp(ctypes.c_void_p(self._ts_comm.data_ptr()), self._ts_cap,
-                           ctypes.c_void_p(self.comm.stream.cuda_stream))
+                           ctypes.c_void_p(comm_stream.cuda_stream))
             _lib.count_launch(2)
         self.comm.finalize()
         self._buffer_sync_pending = False
@@ -451,8 +531,10 @@ class DistributedDataParallel(nn.Module):
         """Mean time per step by which the gradient reductions outlasted backward compute, from device-side
         timestamps (valid for eager steps and for CUDA-graph replays alike). ``last``: only the most recent N steps
         (at most 256 are kept)."""
+        if self.world == 1:
+            return 0.0
         if self._ts_compute is None:
-            return 0.0 if self.world == 1 else None
+            return None
         torch.cuda.synchronize(self.device)
         tc, tm = self._ts_compute.cpu(), self._ts_comm.cpu()
         n = int(min(tc[0].item(), tm[0].item()))
@@ -469,6 +551,32 @@ class DistributedDataParallel(nn.Module):
         if self._ts_compute is not None:
             self._ts_compute.zero_()
             self._ts_comm.zero_()
+            self._ts_start.zero_()
+
+    def step_anatomy(self, last=None):
+        """Where a training step's time goes, from the device-side stamps of the most recent steps (ms, means):
+        ``period`` = start of a step's forward to the start of the next one; ``fwd_bwd`` = start of forward to the end
+        of backward's last kernel; ``tail`` = how long the last reduction outlasts that (exposed communication);
+        ``gap`` = end of the step's device work to the start of the next step (launch / replay hand-over)."""
+        if self._ts_start is None:
+            return None
+        torch.cuda.synchronize(self.device)
+        ts, tc, tm = self._ts_start.cpu(), self._ts_compute.cpu(), self._ts_comm.cpu()
+        n = int(min(ts[0].item(), tc[0].item(), tm[0].item()))
+        k = min(n, self._ts_cap - 1, last or self._ts_cap)
+        if k < 2:
+            return None
+        cap = self._ts_cap
+        per, busy, tail, gap = [], [], [], []
+        for i in range(n - k, n - 1):
+            s0, s1 = int(ts[1 + i % cap]), int(ts[1 + (i + 1) % cap])
+            c, m = int(tc[1 + i % cap]), int(tm[1 + i % cap])
+            per.append((s1 - s0) / 1e6)
+            busy.append((c - s0) / 1e6)
+            tail.append(max(0, m - c) / 1e6)
+            gap.append((s1 - max(c, m)) / 1e6)
+        f = lambda v: round(sum(v) / len(v), 4)   # noqa: E731
+        return {"period": f(per), "fwd_bwd": f(busy), "tail": f(tail), "gap": f(gap), "steps": len(per)}
 
     # ------------------------------------------------------------------ per-bucket trace (B200DDP_TRACE=1)
     def _stamp(self, key, stream):
@@ -539,6 +647,13 @@ class DistributedDataParallel(nn.Module):
         for h in self._hooks:
             h.remove()
         self.comm.window.close()
+
+    def __del__(self):
+        try:
+            if not getattr(self, "_closed", True):
+                self.close()
+        except Exception:  # noqa: BLE001  (interpreter shutdown)
+            pass
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         out = super().load_state_dict(state_dict, strict=strict, **kw)

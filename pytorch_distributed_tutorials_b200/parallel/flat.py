@@ -80,6 +80,7 @@ class FlatParameterStore:
         self.optimizer = None  # set by optim.SGD when it is asked to fuse the update into the reduction
         self._shadow_versions = None
         self.shadow_fresh = False
+        self._numel = {id(p): p.numel() for p in self.params}
         with torch.no_grad():
             for b in self.buckets:
                 for p, off in zip(b.params, b.offsets):
@@ -92,6 +93,42 @@ class FlatParameterStore:
                         gv = _view_like(b.g32, off, p)
                         gv.copy_(p.grad)
                         p.grad = gv
+
+    def rebuild(self, params, bucket_of_param, grad_alloc=None):
+        """Re-bucket the same parameters in a new order (DDP's one-off rebuild in observed gradient-ready order):
+        fresh flat buffers, values, live gradients and momentum carried over, every parameter re-pointed."""
+        old_slot = self.slot
+        old_mom = {pid: (b.mom[off:off + self._numel[pid]] if b.mom is not None else None)
+                   for pid, (b, off) in old_slot.items()} if hasattr(self, "_numel") else {}
+        self.params = list(params)
+        nb = (max(bucket_of_param) + 1) if len(bucket_of_param) else 0
+        groups = [[] for _ in range(nb)]
+        for p, b in zip(self.params, bucket_of_param):
+            groups[b].append(p)
+        had_mom = any(b.mom is not None for b in self.buckets)
+        self.buckets = [Bucket(i, g, self.device, grad_alloc) for i, g in enumerate(groups)]
+        self.slot = {}
+        self.index = {id(p): i for i, p in enumerate(self.params)}
+        self.bucket_of_param = list(bucket_of_param)
+        with torch.no_grad():
+            for b in self.buckets:
+                if had_mom:
+                    b.mom = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
+                for p, off in zip(b.params, b.offsets):
+                    view = _view_like(b.p32, off, p)
+                    view.copy_(p.data)
+                    p.data = view
+                    self.slot[id(p)] = (b, off)
+                    if p.grad is not None:
+                        gv = _view_like(b.g32, off, p)
+                        gv.copy_(p.grad)
+                        p.grad = gv
+                    om = old_mom.get(id(p))
+                    if om is not None and b.mom is not None:
+                        b.mom[off:off + p.numel()].copy_(om)
+        self._numel = {id(p): p.numel() for p in self.params}
+        self.shadow_fresh = False
+        self._shadow_versions = None
 
     # ------------------------------------------------------------------ views
     def grad_view(self, p):

@@ -44,28 +44,34 @@ def _release(res):
     res["released"] = True
     try:
         L = _lib.lib()
+        errs = res.setdefault("errors", [])
+
+        def call(what, rc):
+            if rc != 0:
+                errs.append((what, rc))
+
         if torch.cuda.is_available():
             torch.cuda.synchronize(res["device"])
         nbytes = ctypes.c_longlong(res["nbytes"])
         if res["transport"] == "vmm":
             if res.get("mc_handle") is not None:
                 if res.get("mc_bound"):
-                    L.b2_mc_unbind(ctypes.c_ulonglong(res["mc_handle"]), res["device"], nbytes)
+                    call("mc_unbind", L.b2_mc_unbind(ctypes.c_ulonglong(res["mc_handle"]), res["device"], nbytes))
                 if res.get("mc_ptr"):
-                    L.b2_vmm_unmap(ctypes.c_void_p(res["mc_ptr"]), nbytes)
-                L.b2_vmm_release(ctypes.c_ulonglong(res["mc_handle"]))
+                    call("mc_unmap", L.b2_vmm_unmap(ctypes.c_void_p(res["mc_ptr"]), nbytes))
+                call("mc_release", L.b2_vmm_release(ctypes.c_ulonglong(res["mc_handle"])))
             for ptr_, h in res.get("peers", []):
-                L.b2_vmm_unmap(ctypes.c_void_p(ptr_), nbytes)
-                L.b2_vmm_release(ctypes.c_ulonglong(h))
+                call("peer_unmap", L.b2_vmm_unmap(ctypes.c_void_p(ptr_), nbytes))
+                call("peer_release", L.b2_vmm_release(ctypes.c_ulonglong(h)))
             if res.get("local_ptr"):
-                L.b2_vmm_unmap(ctypes.c_void_p(res["local_ptr"]), nbytes)
+                call("local_unmap", L.b2_vmm_unmap(ctypes.c_void_p(res["local_ptr"]), nbytes))
             if res.get("local_handle") is not None:
-                L.b2_vmm_release(ctypes.c_ulonglong(res["local_handle"]))
+                call("local_release", L.b2_vmm_release(ctypes.c_ulonglong(res["local_handle"])))
         elif res["transport"] == "ipc":
             for ptr_, _ in res.get("peers", []):
-                L.b2_ipc_close(ctypes.c_void_p(ptr_))
+                call("ipc_close", L.b2_ipc_close(ctypes.c_void_p(ptr_)))
             if res.get("local_ptr"):
-                L.b2_ipc_free(ctypes.c_void_p(res["local_ptr"]))
+                call("ipc_free", L.b2_ipc_free(ctypes.c_void_p(res["local_ptr"])))
     except Exception:  # noqa: BLE001  (interpreter shutdown: the driver reclaims everything anyway)
         pass
 

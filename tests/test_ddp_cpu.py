@@ -131,3 +131,65 @@ def test_no_sync_and_checkpoint_roundtrip(tmp_path):
         assert r["same"]
         assert r["dtypes"] == ["torch.float32", "torch.int64"]
         assert r["nkeys"] == 122
+
+
+class _OutOfOrder(nn.Module):
+    """Registration order (head, tail, mid) differs from the order of use (tail -> mid -> head): reversed
+    registration order is the wrong guess for the gradient-ready order."""
+
+    def __init__(self):
+        super().__init__()
+        self.head = nn.Linear(48, 10)
+        self.tail = nn.Linear(20, 64)
+        self.mid = nn.Linear(64, 48)
+
+    def forward(self, x):
+        return self.head(torch.tanh(self.mid(torch.relu(self.tail(x)))))
+
+
+def _rebuild(rank, world):
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    from pytorch_distributed_tutorials_b200 import optim
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    torch.manual_seed(0)
+    net = _OutOfOrder()
+    ref = _OutOfOrder()
+    ref.load_state_dict(net.state_dict())
+    ours = DistributedDataParallel(net, bucket_cap_mb=0.004)        # ~4 KB buckets: several of them
+    theirs = TorchDDP(ref, bucket_cap_mb=0.004)
+    o1 = optim.SGD(ours.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    o2 = torch.optim.SGD(theirs.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    names = {id(p): n for n, p in net.named_parameters()}
+    before = [names[id(p)] for p in ours.ordered_params]
+    g = torch.Generator().manual_seed(5 + rank)
+    worst = 0.0
+    for _ in range(4):
+        x = torch.randn(16, 20, generator=g)
+        y = torch.randint(0, 10, (16,), generator=g)
+        for m, o in ((ours, o1), (theirs, o2)):
+            o.zero_grad()
+            nn.functional.cross_entropy(m(x), y).backward()
+            o.step()
+        worst = max(worst, max((a - b).abs().max().item() for a, b in zip(net.parameters(), ref.parameters())))
+    after = [names[id(p)] for p in ours.ordered_params]
+    flat = torch.cat([p.detach().reshape(-1) for p in net.parameters()])
+    other = flat.clone()
+    dist.broadcast(other, 0)
+    sd = o1.state_dict()
+    return {"before": before, "after": after, "rebuilt": ours.rebuilt_buckets, "maxdiff": worst,
+            "ident": bool(torch.equal(flat, other)), "nbuckets": len(ours.store.buckets),
+            "order_bcasts": len([c for c in ours.collective_log() if c[0] == "broadcast_order"]),
+            "momentum_ok": all("momentum_buffer" in s for s in sd["state"].values())}
+
+
+def test_buckets_are_rebuilt_in_observed_gradient_ready_order():
+    """K5: a generic module starts from reversed registration order; after the first backward the buckets follow
+    the order the gradients really arrived in (rank 0's, broadcast), and training still tracks torch DDP."""
+    for r in run_ranks(_rebuild, world=2, backend="gloo", timeout=300):
+        assert r["before"] == ["mid.bias", "mid.weight", "tail.bias", "tail.weight", "head.bias", "head.weight"], r
+        assert r["rebuilt"] and r["order_bcasts"] == 1
+        # gradients arrive last layer first: head, then mid, then tail (bias / weight order is autograd's)
+        assert [n.split(".")[0] for n in r["after"]] == ["head", "head", "mid", "mid", "tail", "tail"], r
+        assert r["ident"] and r["momentum_ok"] and r["nbuckets"] > 1
+        assert r["maxdiff"] < 1e-5, r

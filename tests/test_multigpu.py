@@ -426,20 +426,23 @@ def test_generic_module_through_p2p_backend_matches_torch_ddp():
 
 def _teardown(rank, world):
     """Construct / destroy the wrapper many times: the symmetric windows (VMM allocations mapped on every peer,
-    multicast binding) must really be released - device memory in use stays flat."""
+    multicast binding) must really be released - device memory held outside torch's caching allocator stays flat."""
     import gc
     import torch.distributed as dist
     from pytorch_distributed_tutorials_b200.models.resnet import resnet18
     from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    from pytorch_distributed_tutorials_b200.parallel.ddp import _LIVE
     dev = torch.device("cuda", rank)
     x = torch.randn(4, 3, 32, 32, device=dev)
-    used = []
-    for it in range(20):
+    outside, errors, live, win_mib = [], [], [], 0
+    for it in range(12):
         net = resnet18().to(dev)
         ddp = DistributedDataParallel(net, device_ids=[rank])
         ddp(x).sum().backward()
         torch.cuda.synchronize()
         dist.barrier()
+        res = ddp.comm.window._res
+        win_mib = res["nbytes"] >> 20
         if it % 2 == 0:
             ddp.close()                       # explicit
             rm = net.bn1.running_mean.clone() # the module survives its wrapper: buffers were moved out of the window
@@ -448,17 +451,22 @@ def _teardown(rank, world):
         gc.collect()
         torch.cuda.synchronize()
         dist.barrier()
+        errors += res.get("errors", [])
+        live.append((len(_LIVE), bool(res.get("released"))))
+        torch.cuda.empty_cache()
         free, total = torch.cuda.mem_get_info(dev)
-        used.append((total - free) >> 20)
-    return {"used_mib": used}
+        outside.append(((total - free) - torch.cuda.memory_reserved(dev)) >> 20)
+    return {"outside_mib": outside, "errors": errors, "live": live, "window_mib": win_mib}
 
 
 def test_symmetric_windows_are_released():
     _need(2)
     for r in run_ranks(_teardown, world=2, backend="b200", timeout=600):
-        u = r["used_mib"]
-        # one window is ~200 MiB (x2 for the peer mapping's physical pages being kept alive): a leak of 20 shows
-        assert max(u[4:]) - min(u[4:]) < 96, u
+        u = r["outside_mib"]
+        assert not r["errors"], r
+        assert all(rel for _, rel in r["live"]), r
+        # memory outside torch's allocator (CUDA context + windows) must not grow by a window per iteration
+        assert max(u[2:]) - min(u[2:]) < max(32, r["window_mib"] // 2), r
 
 
 def _slow_rank0(rank, world):
