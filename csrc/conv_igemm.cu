@@ -1540,6 +1540,11 @@ static int conv_fprop_impl(const void* x, const void* w, const float* bias, void
                            void* stream) {
   if (stats_blocks) *stats_blocks = 0;
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
+  // narrow 3x3 / stride 1 layers: weight-stationary kernel that loads every input pixel once (csrc/conv3x3.cu)
+  if (KH == 3 && KW == 3 && stride == 1 && pad == 1 && !bias && g_impl == 2 && g_act_mode != ACT_GATHER &&
+      b2_conv_halo_supported(N, H, W, Cin, Cout))
+    return b2_conv3x3_halo(0, x, w, y, N, H, W, Cin, Cout, g_fuse_stats ? stats : nullptr, stats_blocks, nullptr,
+                           nullptr, nullptr, stream);
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * Ho * Wo, K = KH * KW * Cin;
   const int bn = bn_for(Cout);
@@ -1700,6 +1705,12 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
                            int KW, int stride, int pad, const void* add, const void* mask, void* stream,
                            const DgradBn* bnreq) {
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
+  if (KH == 3 && KW == 3 && stride == 1 && pad == 1 && !add && !mask && g_impl == 2 && g_act_mode != ACT_GATHER &&
+      b2_conv_halo_supported(N, H, W, Cout, Cin)) {
+    const bool st = bnreq && g_fuse_stats;
+    return b2_conv3x3_halo(1, dy, w, dx, N, H, W, Cin, Cout, st ? bnreq->partial : nullptr, st ? bnreq->blocks : nullptr,
+                           st ? bnreq->y : nullptr, st ? bnreq->mask : nullptr, st ? bnreq->mean : nullptr, stream);
+  }
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int M = N * H * W;
   const int cpb = (Cout + 63) / 64;

@@ -87,17 +87,21 @@ B2_DEVICE uint64_t global_timer_ns() {
 struct SpinGuard {
   uint64_t t0 = 0;
   uint32_t polls = 0;
-  B2_DEVICE void tick() {
+  B2_DEVICE void tick(uint64_t limit_ns) {
     if ((++polls & 0x3FFu) == 0) {
       const uint64_t now = global_timer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > spin_timeout_ns()) __trap();
+      else if (now - t0 > limit_ns) __trap();
     }
   }
+  B2_DEVICE void tick() { tick(spin_timeout_ns()); }   // waits on other GPUs: the configurable (long) bound
 };
+// Waits on mbarriers are waits on this CTA's own TMA / tensor-core / warp traffic: microseconds when the protocol is
+// right, forever when it is not - a fixed short bound, independent of the (minutes-long) cross-GPU one.
+constexpr uint64_t kMbarTimeoutNs = 20000000000ull;   // 20 s
 B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
   SpinGuard guard;
-  while (!mbar_try_wait(bar, parity)) guard.tick();
+  while (!mbar_try_wait(bar, parity)) guard.tick(kMbarTimeoutNs);
 }
 
 // ---------------------------------------------------------------- proxies / fences

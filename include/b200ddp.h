@@ -77,6 +77,18 @@ int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, i
 int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N, int H, int W,
                   int Cin, int Cout, int KH, int KW, int stride, int pad, int accumulate, void* stream);
 int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes);
+/* 3x3 / stride 1 / pad 1 with 64 or 128 reduction channels (csrc/conv3x3.cu): weight-stationary kernel - the nine taps
+ * of a CTA's 64 output columns stay in shared memory, every tile's input rows (+ halo) are loaded ONCE and the taps are
+ * nine tcgen05.mma passes over shifted windows of that slab. b2_conv_fprop[_stats] / b2_conv_dgrad[_bnstats] route the
+ * shapes b2_conv_halo_supported(N, H, W, K = reduction channels, Ncols = output columns) accepts through it
+ * (b2_conv_set_halo(0) switches that off). dgrad != 0: src = dy, dst = dx. stats: one partial row per CTA.
+ * Reference: resnet/main.py:76 (conv2 of every torchvision BasicBlock / Bottleneck in layer1 and layer2 -> cuDNN). */
+int b2_conv_halo_supported(int N, int H, int W, int K, int Ncols);
+int b2_conv3x3_halo(int dgrad, const void* src, const void* w, void* dst, int N, int H, int W, int Cin, int Cout,
+                    float* stats, int* stats_blocks, const void* bwd_y, const void* bwd_mask, const float* bwd_mean,
+                    void* stream);
+void b2_conv_set_halo(int on);
+void b2_conv_set_halo_debug(int bits);
 /* Debug/tuning: force the N tile (64/128/256); 0 = automatic. */
 void b2_conv_set_tile_n(int bn);
 /* Debug/tuning: staging of k>1 / strided activations: -1 auto (TMA im2col), 1 = cp.async gather. */

@@ -29,6 +29,9 @@ CONV_SHAPES = [  # ci, co, k, s, p, H, N
     # the sizes that are timed - 1x1 64->256 @56, 3x3 256 @14, strided 3x3 128 @56, strided 1x1 256->512 @56
     (64, 256, 1, 1, 0, 56, 256), (256, 256, 3, 1, 1, 14, 256), (128, 128, 3, 2, 1, 56, 256),
     (256, 512, 1, 2, 0, 56, 256),
+    # weight-stationary halo kernel (csrc/conv3x3.cu): two k-blocks, rows that do not divide into tiles, two column
+    # tiles in dgrad, a frame narrower than 128 rows
+    (128, 128, 3, 1, 1, 28, 8), (64, 128, 3, 1, 1, 14, 5), (128, 64, 3, 1, 1, 9, 2), (128, 128, 3, 1, 1, 28, 256),
 ]
 
 
@@ -259,7 +262,9 @@ def test_stem_conv_via_im2col():
 @pytest.mark.parametrize("ci,co,k,s,p,H,N", [(64, 256, 1, 1, 0, 56, 4), (256, 256, 3, 1, 1, 14, 8),
                                                (512, 2048, 1, 1, 0, 7, 5), (128, 128, 3, 2, 1, 28, 3),
                                                (256, 64, 1, 1, 0, 56, 2), (64, 64, 3, 1, 1, 56, 16),
-                                               (512, 2048, 1, 1, 0, 7, 64), (256, 512, 1, 2, 0, 56, 16)])
+                                               (512, 2048, 1, 1, 0, 7, 64), (256, 512, 1, 2, 0, 56, 16),
+                                               (128, 128, 3, 1, 1, 28, 5), (64, 128, 3, 1, 1, 14, 3),
+                                               (128, 64, 3, 1, 1, 9, 2), (64, 64, 3, 1, 1, 56, 256)])
 def test_conv_epilogue_bn_statistics(ci, co, k, s, p, H, N):
     """The persistent fprop kernel also accumulates per-channel sum / sum of squares of the bf16 output."""
     from pytorch_distributed_tutorials_b200.ops import conv, native
@@ -352,7 +357,8 @@ def test_conv_dgrad_fan_in_relu_mask_and_bn_backward_sums(ci, co, k, p, H, N):
 
 
 @pytest.mark.parametrize("ci,co,k,p,H,N", [(64, 256, 1, 0, 28, 4), (128, 128, 3, 1, 14, 3), (256, 1024, 1, 0, 14, 5),
-                                            (512, 512, 3, 1, 7, 6)])
+                                            (512, 512, 3, 1, 7, 6), (64, 64, 3, 1, 56, 2), (128, 64, 3, 1, 28, 3),
+                                            (64, 128, 3, 1, 9, 2), (128, 128, 3, 1, 28, 64)])
 def test_conv_dgrad_produces_bn_backward_sums(ci, co, k, p, H, N):
     """The dgrad kernel's statistics warps leave sum(g), sum(g*(y-mean)) per channel of dx (g = mask ? dx : 0)."""
     from pytorch_distributed_tutorials_b200.ops import conv, native
