@@ -165,6 +165,16 @@ def build_ours(args, local_rank, world):
     return step, ddp
 
 
+def _numa_note():
+    from pytorch_distributed_tutorials_b200.utils import affinity
+    last = affinity.LAST
+    if last["node"] is None:
+        return "unpinned (platform does not report the GPU's NUMA node)"
+    if last["cpus"] is None:
+        return "node %d, affinity left alone" % last["node"]
+    return "node %d, %d cpus" % (last["node"], last["cpus"])
+
+
 def replica_checksum(ddp):
     """Bit-level checksum of this rank's flat fp32 parameters (wrapping int64 sum of the raw words)."""
     tot = 0
@@ -331,10 +341,13 @@ def main():
         exposed = ddp.exposed_comm_ms(last=args.steps) if (args.impl == "ours" and hasattr(ddp, "exposed_comm_ms")) \
             else None
         anatomy = ddp.step_anatomy(last=args.steps) if (args.impl == "ours" and hasattr(ddp, "step_anatomy")) else None
-        if len(clocks.rows) < 2:                    # very short runs: keep the load on until two samples exist
-            t_wait = time.monotonic()
-            while len(clocks.rows) < 2 and time.monotonic() - t_wait < 3.0:
-                dev_step(0)
+        if ms_total < 500.0:
+            # very short timed regions (ResNet-18 on 32x32 images: ~1 ms per step): keep the same load on for about
+            # 0.8 s more so that the clock sampler (200 ms period) sees it. The number of extra steps is derived from
+            # the max-over-ranks time, i.e. it is the SAME on every rank - every step is a collective.
+            n_extra = int(800.0 / max(ms_total / args.steps, 0.05))
+            for i in range(n_extra):
+                dev_step(i)
             torch.cuda.synchronize()
             t_end = time.monotonic()
     clk = clocks.summary(t_begin, t_end)
@@ -402,7 +415,9 @@ def main():
     # ---- communication overhead of backward, same probe on both arms (runs last: it desynchronises nothing that
     #      is measured afterwards)
     overhead = None
-    if world > 1 and not args.no_comm_probe:
+    if world > 1 and not args.no_comm_probe and args.impl == "reference":
+        # (our arm's figure is measured inside the replayed graph; an eager with/without-sync probe would time Python
+        #  launches and, without sync, an optimizer that is no longer fused into backward - not the product path)
         overhead = backward_comm_overhead(ddp, ddp._bench_parts, xs[0], ys[0], world,
                                           autocast=(args.impl == "reference" and args.ref_variant == "r1"))
         if args.impl == "reference":
@@ -424,6 +439,7 @@ def main():
                        "sync_bn": bool(args.sync_bn),
                        "l2": "per-step inputs (%.0f MB/GPU) exceed the 126 MB L2; no explicit flush" %
                              (args.batch * 3 * args.image_size ** 2 * 4 / 1e6),
+                       "numa_pin": _numa_note() if args.impl == "ours" else "none (the reference does not pin)",
                        "backend": getattr(ddp, "backend", "torch-ddp/nccl" if world > 1 else "none"),
                        "cuda_graph": bool(getattr(getattr(ddp, "_bench_step", None), "captures", 0))},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "ours" else 0,

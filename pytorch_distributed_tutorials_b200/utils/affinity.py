@@ -53,12 +53,16 @@ def gpu_numa_node(index):
     return node if node >= 0 else None
 
 
+LAST = {"node": None, "cpus": None}   # what the most recent pin_to_gpu_numa_node() call found / did (diagnostics)
+
+
 def pin_to_gpu_numa_node(index, verbose=False):
     """Restrict this process to the CPUs of the GPU's NUMA node. Returns the CPU set used (None = left alone:
     single-node host, sysfs not readable, or the node's CPUs are outside the current cgroup's allowance)."""
     if not hasattr(os, "sched_setaffinity"):
         return None
     node = gpu_numa_node(index)
+    LAST["node"] = node
     if node is None:
         return None
     cpus = _parse_cpulist(_read("/sys/devices/system/node/node%d/cpulist" % node))
@@ -73,6 +77,7 @@ def pin_to_gpu_numa_node(index, verbose=False):
         os.sched_setaffinity(0, cpus)
     except OSError:
         return None
+    LAST["cpus"] = len(cpus)
     if verbose:
         print("[b200ddp] cuda:%d -> NUMA node %d, %d CPUs" % (index, node, len(cpus)), flush=True)
     return cpus

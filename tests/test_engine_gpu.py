@@ -74,10 +74,17 @@ def test_resnet50_full_depth_sane():
     out32 = ref.forward_reference(x)
     nn.functional.cross_entropy(out32, y).backward()
     assert _cos(out, out32) > 0.95
+    ratios = []
     for (n, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
         assert p.grad is not None and torch.isfinite(p.grad).all(), n
         a, b = p.grad.float().norm().item(), q.grad.float().norm().item()
-        assert 0.3 * b <= a <= 3.0 * b + 1e-6, (n, a, b)
+        ratios.append((a / max(b, 1e-12), n))
+    # bf16 activations against an fp32 run at full depth: every gradient norm within 25 % (calibrated on B200: the
+    # worst layers are the deepest 1x1 convolutions), the median within 5 %
+    lo, hi = min(ratios), max(ratios)
+    med = sorted(r for r, _ in ratios)[len(ratios) // 2]
+    assert lo[0] > 0.75 and hi[0] < 1.33, (lo, hi)
+    assert 0.95 < med < 1.05, med
 
 
 def test_eval_mode_with_grad_uses_running_statistics_in_backward():
@@ -189,8 +196,10 @@ def test_training_loop_with_wrapper_and_fused_sgd_single_gpu():
         opt_r.step()
         theirs.append(lr_.item())
     assert ours[-1] < ours[0] * 0.8, ours          # it learns
-    assert abs(ours[0] - theirs[0]) < 0.05 * theirs[0]
-    assert abs(ours[-1] - theirs[-1]) < 0.35 * max(theirs[-1], 0.5), (ours, theirs)
+    # step by step against the stock path under bf16 autocast (the engine's own numerical twin): within 5 %
+    # (floor 0.02 for losses that have already collapsed towards zero)
+    for a_, b_ in zip(ours, theirs):
+        assert abs(a_ - b_) < max(0.05 * b_, 0.02), (ours, theirs)
     sd = opt.state_dict()
     assert len(sd["state"]) == 62 and "momentum_buffer" in sd["state"][0]
     keys = list(ddp.state_dict().keys())

@@ -226,8 +226,8 @@ def test_ddp_p2p_trains_like_torch_ddp(world, sync_bn):
         assert r["n_allreduce"] == 5 * len(bk)
         assert r["exposed"] is not None and r["exposed"] >= 0.0
         assert r["ours"][-1] < r["ours"][0]
-        assert abs(r["ours"][0] - r["theirs"][0]) < 0.05 * r["theirs"][0], r
-        assert abs(r["ours"][-1] - r["theirs"][-1]) < 0.35 * max(r["theirs"][-1], 0.5), r
+        for a_, b_ in zip(r["ours"], r["theirs"]):      # every step within 5 % of torch DDP under bf16 autocast
+            assert abs(a_ - b_) < max(0.05 * b_, 0.02), r
 
 
 def _syncbn_stats(rank, world):
