@@ -28,7 +28,7 @@ namespace b2 {
 
 constexpr int kHeadCluster = 8;        // CTAs per cluster = class tiles of 128 (covers up to 1024 classes)
 constexpr int kHeadImgs = 16;          // images per cluster = MMA N
-constexpr int kHeadThreads = 256;      // 8 warps: all pool; then warp 0 = TMA, warp 1 = MMA, warps 4-7 = epilogue
+constexpr int kHeadThreads = 512;      // 16 warps: one image each while pooling; then warp 0 = TMA, 1 = MMA, 4-7 = epilogue
 constexpr int kHeadStages = 6;         // weight ring: 6 x 16 KB
 constexpr int kHeadStageBytes = 128 * 128;   // 128 classes x 64 bf16
 constexpr int kHeadMaxC = 2048;
@@ -114,6 +114,18 @@ __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThre
       if (img < N) {
         const __nv_bfloat16* src = x + ((long long)img * HW) * C + c_lane;
         int p = psub;
+        for (; p + 13 * P < HW; p += 14 * P) {  // 14 independent 16-byte loads in flight per lane
+          uint4 u[14];
+#pragma unroll
+          for (int q = 0; q < 14; ++q) u[q] = ld_nc_v4(src + (long long)(p + q * P) * C);
+#pragma unroll
+          for (int q = 0; q < 14; ++q) {
+            const float2 a0 = unpack_bf16x2(u[q].x), a1 = unpack_bf16x2(u[q].y), a2 = unpack_bf16x2(u[q].z),
+                         a3 = unpack_bf16x2(u[q].w);
+            acc[0] += a0.x; acc[1] += a0.y; acc[2] += a1.x; acc[3] += a1.y;
+            acc[4] += a2.x; acc[5] += a2.y; acc[6] += a3.x; acc[7] += a3.y;
+          }
+        }
         for (; p + 6 * P < HW; p += 7 * P) {    // 7 independent 16-byte loads in flight per lane
           uint4 u[7];
 #pragma unroll
@@ -190,8 +202,8 @@ __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThre
       }
       umma_commit(&s.accum);
     }
-  } else if (warp >= 4) {
-    // ---- epilogue: TMEM lane = class, column = image
+  } else if (warp >= 4 && warp < 8) {
+    // ---- epilogue: TMEM lane = class, column = image (warps 4..7: TMEM lane quadrant = warp % 4)
     mbar_wait(&s.accum, 0);
     tc_fence_after();
     const int q = warp - 4;                       // TMEM lane quarter this warp may read
