@@ -65,7 +65,11 @@ extern "C" b2_reducer* b2_reducer_create(int n_params, const int* bucket_of_para
   return r;
 }
 
-extern "C" void b2_reducer_destroy(b2_reducer* r) { delete r; }
+extern "C" void b2_reducer_release_launch_state(b2_reducer* r);
+extern "C" void b2_reducer_destroy(b2_reducer* r) {
+  b2_reducer_release_launch_state(r);
+  delete r;
+}
 
 // prepare_for_backward: every bucket waits for all of its parameters again.
 extern "C" void b2_reducer_reset(b2_reducer* r) {
@@ -97,4 +101,105 @@ extern "C" long long b2_reducer_iterations(const b2_reducer* r) { return r->iter
 extern "C" int b2_reducer_ready_order(const b2_reducer* r, int* out) {
   std::memcpy(out, r->ready_order.data(), r->ready_order.size() * sizeof(int));
   return (int)r->ready_order.size();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Native launch path (P2P backend): per-bucket launch descriptors are registered once; marking a parameter ready then
+// launches, from C++, the fused all-reduce(+SGD) kernel of every bucket that became launchable - event record on the
+// compute stream, wait on the communication stream, kernel launch - and the end-of-backward join is one call as well.
+// (c10d::Reducer::mark_variable_ready -> mark_bucket_ready -> all_reduce_bucket and finalize_backward of the reference
+// stack, reference resnet/main.py:80,123; Python keeps the tensors, C++ does the sequencing and the launches.)
+#include <cuda_runtime.h>
+
+struct b2_bucket_launch {
+  b2_bucket_desc d;
+  cudaEvent_t ready = nullptr;
+  bool set = false;
+};
+struct b2_reducer_launch_state {
+  std::vector<b2_bucket_launch> buckets;
+  cudaEvent_t joined = nullptr;
+};
+static std::mutex g_ls_mu;
+static std::vector<std::pair<const b2_reducer*, b2_reducer_launch_state*>> g_ls;
+
+static b2_reducer_launch_state* launch_state(const b2_reducer* r, bool create) {
+  std::lock_guard<std::mutex> g(g_ls_mu);
+  for (auto& kv : g_ls)
+    if (kv.first == r) return kv.second;
+  if (!create) return nullptr;
+  auto* s = new b2_reducer_launch_state();
+  s->buckets.resize(r->n_buckets);
+  g_ls.emplace_back(r, s);
+  return s;
+}
+
+extern "C" int b2_reducer_set_bucket(b2_reducer* r, int bucket, const b2_bucket_desc* desc) {
+  if (!r || !desc || bucket < 0 || bucket >= r->n_buckets) return cudaErrorInvalidValue;
+  b2_reducer_launch_state* s = launch_state(r, true);
+  b2_bucket_launch& b = s->buckets[bucket];
+  b.d = *desc;
+  if (!b.ready) {
+    cudaError_t e = cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming);
+    if (e != cudaSuccess) return e;
+  }
+  if (!s->joined) {
+    cudaError_t e = cudaEventCreateWithFlags(&s->joined, cudaEventDisableTiming);
+    if (e != cudaSuccess) return e;
+  }
+  b.set = true;
+  return 0;
+}
+
+extern "C" void b2_reducer_release_launch_state(b2_reducer* r) {
+  std::lock_guard<std::mutex> g(g_ls_mu);
+  for (size_t i = 0; i < g_ls.size(); ++i) {
+    if (g_ls[i].first != r) continue;
+    for (auto& b : g_ls[i].second->buckets)
+      if (b.ready) cudaEventDestroy(b.ready);
+    if (g_ls[i].second->joined) cudaEventDestroy(g_ls[i].second->joined);
+    delete g_ls[i].second;
+    g_ls.erase(g_ls.begin() + i);
+    return;
+  }
+}
+
+// mark parameter idx ready; launch what became launchable. launched[] receives the bucket indices, the return value
+// their number (< 0: -1 marked twice, -2 bad index, -3 a bucket without a descriptor, -100 - cudaError otherwise).
+extern "C" int b2_reducer_mark_ready_launch(b2_reducer* r, int idx, int fused, float lr, float momentum,
+                                            float weight_decay, int first_step, const float* hyper_dev,
+                                            void* compute_stream, void* comm_stream, int* launched) {
+  const int n = b2_reducer_mark_ready(r, idx, launched);
+  if (n <= 0) return n;
+  b2_reducer_launch_state* s = launch_state(r, false);
+  if (!s) return -3;
+  cudaStream_t cs = (cudaStream_t)compute_stream, ms = (cudaStream_t)comm_stream;
+  for (int i = 0; i < n; ++i) {
+    b2_bucket_launch& b = s->buckets[launched[i]];
+    if (!b.set) return -3;
+    cudaError_t e = cudaEventRecord(b.ready, cs);          // the kernels that produced this bucket's gradients ...
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ms, b.ready, 0);   // ... before the reduction reads them
+    if (e != cudaSuccess) return -100 - (int)e;
+    const b2_bucket_desc& d = b.d;
+    int rc;
+    if (d.wire_bf16)
+      rc = b2_allreduce_bf16(&d.ctx, d.mc_base, d.wire_offset_bytes, d.n, d.algo, d.scale, d.g32,
+                             (d.write_grad || !fused) ? d.g32 : nullptr, fused ? d.p32 : nullptr, d.mom, d.shadow, lr,
+                             momentum, weight_decay, first_step, hyper_dev, d.nblocks, comm_stream);
+    else
+      rc = b2_allreduce(&d.ctx, d.mc_base, d.offset_bytes, d.n, d.algo, d.scale, fused ? d.p32 : nullptr, d.mom,
+                        d.shadow, lr, momentum, weight_decay, first_step, hyper_dev, d.write_grad, d.nblocks,
+                        comm_stream);
+    if (rc) return -100 - rc;
+  }
+  return n;
+}
+
+// finalize_backward: everything queued on the compute stream from here on waits for the reductions
+extern "C" int b2_reducer_join(b2_reducer* r, void* compute_stream, void* comm_stream) {
+  b2_reducer_launch_state* s = launch_state(r, false);
+  if (!s || !s->joined) return cudaErrorInvalidValue;
+  cudaError_t e = cudaEventRecord(s->joined, (cudaStream_t)comm_stream);
+  if (e == cudaSuccess) e = cudaStreamWaitEvent((cudaStream_t)compute_stream, s->joined, 0);
+  return (int)e;
 }

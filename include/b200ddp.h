@@ -242,6 +242,33 @@ int b2_reducer_mark_ready(b2_reducer* r, int idx, int* launch);
 int b2_reducer_unlaunched(const b2_reducer* r);
 long long b2_reducer_iterations(const b2_reducer* r);
 int b2_reducer_ready_order(const b2_reducer* r, int* out);
+/* Native launch path: a bucket's all-reduce launch descriptor (what b2_allreduce / b2_allreduce_bf16 need), registered
+ * once per bucket (again after the momentum buffers come into existence or the buckets are rebuilt). With descriptors
+ * in place b2_reducer_mark_ready_launch marks a parameter ready AND launches the fused reduction of every bucket that
+ * became launchable (event on the compute stream -> wait on the communication stream -> kernel), writing the launched
+ * bucket indices to `launched`; b2_reducer_join makes the compute stream wait for the reductions (finalize_backward).
+ * Reference: c10d::Reducer mark_variable_ready / all_reduce_bucket / finalize_backward behind resnet/main.py:80,123. */
+typedef struct b2_bucket_desc {
+  b2_xgpu_ctx ctx;
+  void* mc_base;
+  long long offset_bytes; /* fp32 wire: the bucket inside the window */
+  long long n;            /* fp32 elements */
+  int algo;
+  float scale;
+  float* p32;             /* fused update (used when the call says fused) */
+  float* mom;
+  void* shadow;
+  int write_grad, nblocks;
+  int wire_bf16;          /* 1: b2_allreduce_bf16 with the two fields below */
+  long long wire_offset_bytes;
+  float* g32;
+} b2_bucket_desc;
+int b2_reducer_set_bucket(b2_reducer* r, int bucket, const b2_bucket_desc* desc);
+int b2_reducer_mark_ready_launch(b2_reducer* r, int idx, int fused, float lr, float momentum, float weight_decay,
+                                 int first_step, const float* hyper_dev, void* compute_stream, void* comm_stream,
+                                 int* launched);
+int b2_reducer_join(b2_reducer* r, void* compute_stream, void* comm_stream);
+void b2_reducer_release_launch_state(b2_reducer* r);
 
 /* ------------------------------------------------------------------------------------------------
  * Symmetric-memory runtime and watchdog (csrc/symm.cu).

@@ -30,6 +30,18 @@ from .comm import LocalComm, P2PComm, TorchComm
 from .flat import FlatParameterStore, plan_buckets
 
 MiB = 1 << 20
+
+
+class _BucketDesc(ctypes.Structure):
+    """Mirror of ``b2_bucket_desc`` (include/b200ddp.h): everything the native reducer needs to launch a bucket."""
+    from ..ops.native import XgpuCtx as _Ctx
+    _fields_ = [("ctx", _Ctx), ("mc_base", ctypes.c_void_p), ("offset_bytes", ctypes.c_longlong),
+                ("n", ctypes.c_longlong), ("algo", ctypes.c_int), ("scale", ctypes.c_float),
+                ("p32", ctypes.c_void_p), ("mom", ctypes.c_void_p), ("shadow", ctypes.c_void_p),
+                ("write_grad", ctypes.c_int), ("nblocks", ctypes.c_int), ("wire_bf16", ctypes.c_int),
+                ("wire_offset_bytes", ctypes.c_longlong), ("g32", ctypes.c_void_p)]
+
+
 _LIVE = weakref.WeakSet()   # wrappers whose symmetric windows destroy_process_group() must release
 
 
@@ -224,6 +236,10 @@ class DistributedDataParallel(nn.Module):
             self._ts_comm = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
             self._ts_start = torch.zeros(self._ts_cap + 1, dtype=torch.int64, device=self.device)
         self.trace_buckets = os.environ.get("B200DDP_TRACE", "0") == "1" and backend == "p2p"
+        # native launch path (csrc/reducer.cpp): marking a gradient ready launches the fused reductions from C++
+        self._native_launch = backend == "p2p" and not self.trace_buckets and \
+            os.environ.get("B200DDP_NATIVE_LAUNCH", "1") == "1"
+        self._native_key = None
         self._bucket_rings = {}
         self._buffers_in_sync = bool(init_sync) or self.world == 1   # constructor broadcast done; False after load_state_dict
         self._post_forward_sync = backend == "p2p" and os.environ.get("B200DDP_BUFFER_SYNC", "post") == "post"
@@ -254,6 +270,39 @@ class DistributedDataParallel(nn.Module):
         self._reducer = ctypes.c_void_p(L.b2_reducer_create(n, arr, len(self.store.buckets)))
         self._launch_buf = (ctypes.c_int * max(1, len(self.store.buckets)))()
         self._finalizer = weakref.finalize(self, L.b2_reducer_destroy, self._reducer)
+
+    def _register_native_launch(self):
+        """(Re-)register every bucket's launch descriptor with the native reducer when a buffer address changed
+        (momentum buffers appear with the first fused step; a bucket rebuild replaces everything)."""
+        comm = self.comm
+        key = tuple((b.p32.data_ptr(), b.mom.data_ptr() if b.mom is not None else 0, b.g32.data_ptr())
+                    for b in self.store.buckets)
+        if key == self._native_key:
+            return
+        from .comm import ALGOS
+        algo = comm.algo
+        if algo == ALGOS["multimem"] and not comm.mc_base:
+            algo = ALGOS["twoshot"]
+        L = _lib.lib()
+        for b in self.store.buckets:
+            d = _BucketDesc()
+            ctypes.memmove(ctypes.byref(d.ctx), ctypes.byref(comm.window.ctx(P2PComm.PAD_COMM)), ctypes.sizeof(d.ctx))
+            d.mc_base = comm.mc_base or 0
+            d.offset_bytes = comm.window.offset_of(b.g32)
+            d.n, d.algo, d.scale = b.numel, algo, 1.0 / self.world
+            d.p32, d.mom = b.p32.data_ptr(), (b.mom.data_ptr() if b.mom is not None else 0)
+            d.shadow = b.shadow.data_ptr() if b.shadow is not None else 0
+            d.write_grad, d.nblocks = int(comm.write_grad), comm.nblocks
+            d.wire_bf16 = int(comm.wire == "bf16")
+            if d.wire_bf16:
+                if getattr(b, "wire16", None) is None:
+                    b.wire16 = comm.alloc_tensor(b.numel, torch.bfloat16)
+                d.wire_offset_bytes = comm.window.offset_of(b.wire16)
+            d.g32 = b.g32.data_ptr()
+            e = L.b2_reducer_set_bucket(self._reducer, b.index, ctypes.byref(d))
+            if e:
+                raise _lib.NativeError("b2_reducer_set_bucket failed with CUDA error %d" % e)
+        self._native_key = key
 
     def _record_ready_order(self):
         """After the first synchronised backward: the order in which the gradients actually arrived."""
@@ -286,6 +335,7 @@ class DistributedDataParallel(nn.Module):
         self.bucket_of_param = plan
         self._param_index = {id(p): i for i, p in enumerate(params)}
         self._make_reducer()
+        self._native_key = None
         self.rebuilt_buckets = True
 
     # ------------------------------------------------------------------ buffers
@@ -445,12 +495,46 @@ class DistributedDataParallel(nn.Module):
         if not self._callback_queued:
             self._callback_queued = True
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+        if self._native_launch:
+            return self._mark_ready_native(idx)
         n = _lib.lib().b2_reducer_mark_ready(self._reducer, idx, self._launch_buf)
         if n == -1:
             raise RuntimeError("a parameter was marked ready twice in one iteration (second backward() through "
                                "the same forward? use no_sync() for gradient accumulation)")
         for i in range(n):
             self._launch_bucket(self.store.buckets[self._launch_buf[i]])
+
+    def _fused_sgd_args(self):
+        opt = self.store.optimizer
+        if opt is not None and opt.fuse_with_backward and self.backend in ("p2p", "local") and opt._native_ok():
+            if self._fused_args is None:
+                self._fused_args = opt.prepare_fused(self.store)
+            return self._fused_args
+        return None
+
+    def _mark_ready_native(self, idx):
+        """One C call: mark ready + launch every bucket that became launchable (events, stream wait, kernel)."""
+        sgd = self._fused_sgd_args()
+        if self._native_key is None or sgd is not None:
+            self._register_native_launch()
+        lr, mu, wd, first, hyper = (tuple(sgd) + (None,))[:5] if sgd is not None else (0.0, 0.0, 0.0, 0, None)
+        cur = torch.cuda.current_stream(self.device)
+        n = _lib.lib().b2_reducer_mark_ready_launch(
+            self._reducer, idx, int(sgd is not None), ctypes.c_float(lr), ctypes.c_float(mu), ctypes.c_float(wd),
+            int(first), ctypes.c_void_p(hyper.data_ptr() if hyper is not None else 0),
+            ctypes.c_void_p(cur.cuda_stream), ctypes.c_void_p(self.comm.stream.cuda_stream), self._launch_buf)
+        if n == -1:
+            raise RuntimeError("a parameter was marked ready twice in one iteration (second backward() through "
+                               "the same forward? use no_sync() for gradient accumulation)")
+        if n < -1:
+            raise _lib.NativeError("native bucket launch failed (%d)" % n)
+        opt = self.store.optimizer
+        for i in range(n):
+            b = self.store.buckets[self._launch_buf[i]]
+            self.comm.launch_log.append(("allreduce", b.index))
+            _lib.count_launch()
+            if sgd is not None:
+                opt.note_bucket_updated(b)
 
     def _launch_bucket(self, bucket):
         opt = self.store.optimizer
@@ -489,7 +573,13 @@ class DistributedDataParallel(nn.Module):
             L.b2_timestamp(ctypes.c_void_p(self._ts_comm.data_ptr()), self._ts_cap,
                            ctypes.c_void_p(comm_stream.cuda_stream))
             _lib.count_launch(2)
-        self.comm.finalize()
+        if self._native_launch and self._native_key is not None:
+            e = _lib.lib().b2_reducer_join(self._reducer, ctypes.c_void_p(torch.cuda.current_stream(
+                self.device).cuda_stream), ctypes.c_void_p(self.comm.stream.cuda_stream))
+            if e:
+                raise _lib.NativeError("b2_reducer_join failed with CUDA error %d" % e)
+        else:
+            self.comm.finalize()
         self._buffer_sync_pending = False
         if self._fused_args is not None:
             self.store.mark_params_updated_natively()

@@ -181,8 +181,8 @@ def test_training_loop_with_wrapper_and_fused_sgd_single_gpu():
     ddp = DistributedDataParallel(base, device_ids=[0])
     # a small learning rate: with a large one the single batch is memorised within six steps and the two bf16
     # trajectories (same maths, different rounding) drift apart chaotically - that would test luck, not kernels
-    opt = optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
-    opt_r = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-5)
+    opt = optim.SGD(ddp.parameters(), lr=0.005, momentum=0.9, weight_decay=1e-5, fuse_with_backward=True)
+    opt_r = torch.optim.SGD(ref.parameters(), lr=0.005, momentum=0.9, weight_decay=1e-5)
     crit = CrossEntropyLoss()
     x = torch.randn(32, 3, 32, 32, device=DEV)
     y = torch.randint(0, 10, (32,), device=DEV)
