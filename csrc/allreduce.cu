@@ -219,14 +219,17 @@ __global__ void __launch_bounds__(kArThreads)
   debug_skew(xg.rank, 1);
   {  // own slice: switch-reduced load, scale, multicast store to every rank; the SGD update of this slice is
      // applied straight from the registers (no second read)
+    // eight switch-reduced loads in flight per thread: the NVLS round trip is ~3.5 us, and with four the kernel
+    // trailed torch's multimem_all_reduce_ by 15-25 % between 8 and 32 MB (profiles/comm_bench_w8_r2.log)
+    constexpr int kMcUnroll = 8;
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
-    for (long long vi = s0 + t0; vi < s1; vi += stride * kUnroll) {
-      float4 g[kUnroll];
+    for (long long vi = s0 + t0; vi < s1; vi += stride * kMcUnroll) {
+      float4 g[kMcUnroll];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u)
+      for (int u = 0; u < kMcUnroll; ++u)
         if (vi + u * stride < s1) g[u] = multimem_ld_reduce_f4(mc + (vi + u * stride) * 4);
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < kMcUnroll; ++u) {
         if (vi + u * stride < s1) {
           g[u].x *= scale; g[u].y *= scale; g[u].z *= scale; g[u].w *= scale;
           multimem_st_f4(mc + (vi + u * stride) * 4, g[u]);  // lands in every rank's buffer

@@ -48,45 +48,88 @@ def make_loaders(train_set, test_set, batch_size, sampler, num_workers=8, pin_me
 
 
 class DevicePrefetcher:
-    """Wraps an iterable of (inputs, labels) host batches: copies batch i+1 to the device on a side stream from
-    pinned memory while step i computes. Yields device tensors already safe to use on the current stream."""
+    """Wraps an iterable of (inputs, labels) host batches: copies the next ``depth`` batches to the device on a side
+    stream from pinned memory while the current step computes, and yields device tensors that are safe to use on the
+    current stream.
 
-    def __init__(self, loader, device):
+    The device side is a fixed ring of ``depth + 1`` buffers owned by the prefetcher - no allocation per step (a
+    caching-allocator miss means ``cudaMalloc``, which on a busy or virtualised host costs more than the copy it
+    serves). A buffer is overwritten only after the compute stream has passed the work that was enqueued while its
+    batch was current (an event recorded when the consumer asks for the next batch), so the yielded tensors are valid
+    until ``depth`` further batches have been requested. Batches whose shape differs from the ring's (ragged last
+    batch) get tensors of their own."""
+
+    def __init__(self, loader, device, depth=2):
         self.loader, self.device = loader, torch.device(device)
+        self.depth = max(1, int(depth))
         self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        self._ring = []
 
     def __len__(self):
         return len(self.loader)
 
-    def _stage(self, batch):
+    def _slot_for(self, x, y, index):
+        if len(self._ring) <= index:
+            self._ring.append({"x": torch.empty(x.shape, dtype=x.dtype, device=self.device),
+                               "y": torch.empty(y.shape, dtype=y.dtype, device=self.device), "free": None})
+        slot = self._ring[index]
+        if slot["x"].shape != x.shape or slot["x"].dtype != x.dtype or slot["y"].shape != y.shape \
+                or slot["y"].dtype != y.dtype:
+            return None
+        return slot
+
+    def _stage(self, batch, index):
         x, y = batch[0], batch[1]
         if self.stream is None:
-            return x.to(self.device), y.to(self.device)
+            return {"xd": x.to(self.device), "yd": y.to(self.device), "ev": None, "slot": None, "host": None}
         if not x.is_pinned():
             x = x.pin_memory()
         if not y.is_pinned():
             y = y.pin_memory()
+        slot = self._slot_for(x, y, index)
         with torch.cuda.stream(self.stream):
-            xd = x.to(self.device, non_blocking=True)
-            yd = y.to(self.device, non_blocking=True)
+            if slot is not None:
+                if slot["free"] is not None:
+                    self.stream.wait_event(slot["free"])      # its previous batch has been consumed on the device
+                xd, yd = slot["x"], slot["y"]
+                xd.copy_(x, non_blocking=True)
+                yd.copy_(y, non_blocking=True)
+            else:
+                xd = x.to(self.device, non_blocking=True)
+                yd = y.to(self.device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self.stream)      # this batch's copies only: later copies must not hold the consumer back
-        return xd, yd, ev, (x, y)
+        return {"xd": xd, "yd": yd, "ev": ev, "slot": slot, "host": (x, y)}
 
     def __iter__(self):
+        import collections
         it = iter(self.loader)
-        try:
-            nxt = self._stage(next(it))
-        except StopIteration:
-            return
-        while nxt is not None:
-            cur = nxt
-            try:
-                nxt = self._stage(next(it))
-            except StopIteration:
-                nxt = None
+        staged = collections.deque()
+        nbuf = self.depth + 1
+        counter = [0]
+
+        def fill():
+            while len(staged) < self.depth:
+                try:
+                    batch = next(it)
+                except StopIteration:
+                    return
+                staged.append(self._stage(batch, counter[0] % nbuf))
+                counter[0] += 1
+
+        fill()
+        while staged:
+            cur = staged.popleft()
+            fill()
             if self.stream is not None:
-                torch.cuda.current_stream(self.device).wait_event(cur[2])
-                cur[0].record_stream(torch.cuda.current_stream(self.device))
-                cur[1].record_stream(torch.cuda.current_stream(self.device))
-            yield cur[0], cur[1]
+                cs = torch.cuda.current_stream(self.device)
+                cs.wait_event(cur["ev"])
+                if cur["slot"] is None:
+                    cur["xd"].record_stream(cs)
+                    cur["yd"].record_stream(cs)
+            yield cur["xd"], cur["yd"]
+            # the consumer is back for the next batch: everything it enqueued for this one is on its stream now
+            if self.stream is not None and cur["slot"] is not None:
+                free = torch.cuda.Event()
+                free.record(torch.cuda.current_stream(self.device))
+                cur["slot"]["free"] = free

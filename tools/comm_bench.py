@@ -60,7 +60,9 @@ def main():
              ("r18_b1", 7213056), ("r50_b1", 7875584), ("r152_100MB", 26215424), ("256MiB", 64 << 20)]
     sweep = [(("%dKiB" % (1 << k)), (1 << k) * 256) for k in range(0, 19, 3)]
     rows = []
-    for name, n in sweep + named:
+    only = os.environ.get("COMM_BENCH_ONLY")        # comma-separated row names: a quick re-measurement of a few sizes
+    todo = [(nm, n) for nm, n in sweep + named if not only or nm in only.split(",")]
+    for name, n in todo:
         n = (n + 63) // 64 * 64
         b = _B()
         b.index, b.numel = 0, n
