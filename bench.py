@@ -387,6 +387,8 @@ def main():
         e2e = {"value": global_batch / (ms_e2e / 1e3), "unit": "images/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                "final_loss": float(loss_host[args.steps - 1])}
+        if args.impl == "ours" and hasattr(ddp, "step_anatomy"):
+            e2e["step_anatomy_ms"] = ddp.step_anatomy(last=args.steps)   # where the end-to-end steps' time went
         if args.impl == "ours" and not args.no_bf16_input_e2e:
             # Second, separately labelled end-to-end figure: the same step fed with bf16 host batches (what a
             # DataLoader whose last transform is `.to(torch.bfloat16)` yields; the stem kernel converts to bf16

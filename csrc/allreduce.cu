@@ -219,9 +219,10 @@ __global__ void __launch_bounds__(kArThreads)
   debug_skew(xg.rank, 1);
   {  // own slice: switch-reduced load, scale, multicast store to every rank; the SGD update of this slice is
      // applied straight from the registers (no second read)
-    // eight switch-reduced loads in flight per thread: the NVLS round trip is ~3.5 us, and with four the kernel
-    // trailed torch's multimem_all_reduce_ by 15-25 % between 8 and 32 MB (profiles/comm_bench_w8_r2.log)
-    constexpr int kMcUnroll = 8;
+    // four switch-reduced loads in flight per thread. Eight were tried against torch's multimem_all_reduce_ (which is
+    // 15-25 % faster between 8 and 32 MB): no gain (8.2 MB 43.0 vs 41.6 us, 31.5 MB 118.8 vs 105.0, 100 MB 273.7 vs
+    // 258.9 on two different 8-GPU nodes) - the kernel is not bound by loads in flight at 64 CTAs.
+    constexpr int kMcUnroll = kUnroll;
     const long long s0 = slice * xg.rank, s1 = min(nvec, s0 + slice);
     for (long long vi = s0 + t0; vi < s1; vi += stride * kMcUnroll) {
       float4 g[kMcUnroll];

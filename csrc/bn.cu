@@ -146,11 +146,25 @@ __global__ void __launch_bounds__(kFinThreads)
     xgpu_barrier(xg, /*channel=*/blockIdx.x);
     s = 0.f; ss = 0.f; total = 0.f;
     if (rg == 0) {
-      for (int rk = 0; rk < xg.world; ++rk) {
-        const float* peer = xg.data[rk] + slot_off;
-        s += ld_relaxed_sys_f32(peer + c);
-        ss += ld_relaxed_sys_f32(peer + C + c);
-        total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
+      // all 3 * W peer loads are issued before the first one is consumed (one NVLink round trip, not W of them),
+      // then added in rank order
+      float v0[B2_MAX_WORLD], v1[B2_MAX_WORLD], v2[B2_MAX_WORLD];
+#pragma unroll
+      for (int rk = 0; rk < B2_MAX_WORLD; ++rk) {
+        if (rk < xg.world) {
+          const float* peer = xg.data[rk] + slot_off;
+          v0[rk] = ld_relaxed_sys_f32(peer + c);
+          v1[rk] = ld_relaxed_sys_f32(peer + C + c);
+          v2[rk] = ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
+        }
+      }
+#pragma unroll
+      for (int rk = 0; rk < B2_MAX_WORLD; ++rk) {
+        if (rk < xg.world) {
+          s += v0[rk];
+          ss += v1[rk];
+          total += v2[rk];
+        }
       }
     }
     // No trailing barrier: the caller alternates slot_off between two exchange areas from call to call, and a rank
@@ -387,11 +401,23 @@ __global__ void __launch_bounds__(kFinThreads)
     xgpu_barrier(xg, blockIdx.x);
     sdy = 0.f; sdx = 0.f; total = 0.f;
     if (rg == 0) {
-      for (int rk = 0; rk < xg.world; ++rk) {
-        const float* peer = xg.data[rk] + slot_off;
-        sdy += ld_relaxed_sys_f32(peer + c);
-        sdx += ld_relaxed_sys_f32(peer + C + c);
-        total += ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
+      float v0[B2_MAX_WORLD], v1[B2_MAX_WORLD], v2[B2_MAX_WORLD];   // loads first, adds after (see bn_finalize_kernel)
+#pragma unroll
+      for (int rk = 0; rk < B2_MAX_WORLD; ++rk) {
+        if (rk < xg.world) {
+          const float* peer = xg.data[rk] + slot_off;
+          v0[rk] = ld_relaxed_sys_f32(peer + c);
+          v1[rk] = ld_relaxed_sys_f32(peer + C + c);
+          v2[rk] = ld_relaxed_sys_f32(peer + 2 * C + blockIdx.x);
+        }
+      }
+#pragma unroll
+      for (int rk = 0; rk < B2_MAX_WORLD; ++rk) {
+        if (rk < xg.world) {
+          sdy += v0[rk];
+          sdx += v1[rk];
+          total += v2[rk];
+        }
       }
     }
     // (no trailing barrier: alternating exchange areas, see bn_finalize_kernel)
