@@ -297,12 +297,15 @@ __global__ void __launch_bounds__(kBnThreads, B2_BN_BLOCKS_PER_SM)
 // to the compiler to hoist loads across the unrolled iterations, which the 64-register cap of 4 CTAs/SM prevents:
 // ncu showed the kernel waiting on long_scoreboard at 49 % occupancy and 75 % of the measured HBM peak.
 // BPS = CTAs per SM the register budget is sized for (fewer CTAs, more registers, more loads in flight each).
-template <bool RELU, bool TWO, bool GOUT, int U, int BPS>
+// TWO = 2: the second incoming gradient exists at HALF resolution only - it is the input gradient of a 1x1 / stride 2
+// downsample convolution, non-zero at the even pixels of the [N, qH, qW] grid - and is read from its compact
+// [N, qH/2, qW/2, C] form instead of from a zero-filled full-resolution tensor.
+template <bool RELU, int TWO, bool GOUT, int U, int BPS>
 __global__ void __launch_bounds__(kBnThreads, BPS)
     bn_bwd_reduce_batched_kernel(const __nv_bfloat16* __restrict__ dza, const __nv_bfloat16* __restrict__ dzb,
                                  const unsigned char* __restrict__ mask, const __nv_bfloat16* __restrict__ y,
                                  const float* __restrict__ mean, float* partial, __nv_bfloat16* __restrict__ gout,
-                                 long long M, int C) {
+                                 long long M, int C, int qH, int qW) {
   extern __shared__ float smem[];
   const int C8 = C >> 3, RP = kBnThreads / C8;
   const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
@@ -321,7 +324,18 @@ __global__ void __launch_bounds__(kBnThreads, BPS)
         if (row < M) {
           const long long off = row * C + cv * 8;
           ua[u] = ld_nc_v4(dza + off);
-          if (TWO) ub[u] = ld_nc_v4(dzb + off);
+          if (TWO == 1) ub[u] = ld_nc_v4(dzb + off);
+          if (TWO == 2) {
+            const int w = (int)(row % qW);
+            const long long t = row / qW;
+            const int h = (int)(t % qH);
+            const long long n = t / qH;
+            ub[u] = make_uint4(0u, 0u, 0u, 0u);
+            if (((h | w) & 1) == 0) {
+              const long long qrow = (n * ((qH + 1) >> 1) + (h >> 1)) * ((qW + 1) >> 1) + (w >> 1);
+              ub[u] = ld_nc_v4(dzb + qrow * C + cv * 8);
+            }
+          }
           uy[u] = ld_nc_v4(y + off);
           if (RELU) bits[u] = mask[off >> 3];
         }
@@ -594,7 +608,8 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
 static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
                        void* dy, void* dres, long long M, int C, const float* gamma, const float* mean,
                        const float* invstd, float* dgamma, float* dbeta, int accumulate, int relu, float* coef,
-                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream);
+                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream, int qH = 0,
+                       int qW = 0);
 
 extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
                          void* dy, void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd,
@@ -602,6 +617,18 @@ extern "C" int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, cons
                          const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
   return bn_bwd_impl(dz_a, dz_b, z, relu_mask, y, dy, dres, M, C, gamma, mean, invstd, dgamma, dbeta, accumulate, relu,
                      coef, partial, 0, xg, xg_slot, stream);
+}
+
+// Same with the second incoming gradient at half resolution: dz_b_q is [N, ceil(H/2), ceil(W/2), C] and stands for
+// a full-resolution [N, H, W, C] tensor that is dz_b_q at the even pixels and zero elsewhere (the input gradient of a
+// 1x1 / stride 2 convolution). Needs the 1-bit ReLU mask form and a dres output.
+extern "C" int b2_bn_bwd_q(const void* dz_a, const void* dz_b_q, int H, int W, const void* relu_mask, const void* y,
+                           void* dy, void* dres, long long M, int C, const float* gamma, const float* mean,
+                           const float* invstd, float* dgamma, float* dbeta, int accumulate, int relu, float* coef,
+                           float* partial, const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+  if (!dz_b_q || H <= 0 || W <= 0 || M % ((long long)H * W)) return cudaErrorInvalidValue;
+  return bn_bwd_impl(dz_a, dz_b_q, nullptr, relu_mask, y, dy, dres, M, C, gamma, mean, invstd, dgamma, dbeta,
+                     accumulate, relu, coef, partial, 0, xg, xg_slot, stream, H, W);
 }
 
 // Same, but `partial` already holds partial_blocks rows of [2][C] (sum g, sum g*(y-mean)) - produced by the dgrad
@@ -619,7 +646,8 @@ extern "C" int b2_bn_bwd_partial(const void* dz, const void* z, const void* relu
 static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const void* relu_mask, const void* y,
                        void* dy, void* dres, long long M, int C, const float* gamma, const float* mean,
                        const float* invstd, float* dgamma, float* dbeta, int accumulate, int relu, float* coef,
-                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream) {
+                       float* partial, int given_blocks, const b2_xgpu_ctx* xg, int xg_slot, void* stream, int qH,
+                       int qW) {
   if (!bn_shape_ok(C)) return cudaErrorInvalidValue;
   cudaStream_t st = (cudaStream_t)stream;
   long long rpb;
@@ -638,18 +666,21 @@ static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const 
   } while (0)
 #define REDB(R, T, UU, BPS)                                                                                         \
   do {                                                                                                              \
-    if (dres) bn_bwd_reduce_batched_kernel<R, T, true, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C); \
-    else bn_bwd_reduce_batched_kernel<R, T, false, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C);     \
+    if (dres) bn_bwd_reduce_batched_kernel<R, T, true, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C, qH, qW); \
+    else bn_bwd_reduce_batched_kernel<R, T, false, UU, BPS><<<nblk, kBnThreads, sm, st>>>(a, b, mk, yy, mean, partial, drp, M, C, qH, qW);     \
   } while (0)
 #define REDV(UU, BPS)                                        \
   do {                                                       \
-    if (relu && dzb) REDB(true, true, UU, BPS);              \
-    else if (relu) REDB(true, false, UU, BPS);               \
-    else if (dzb) REDB(false, true, UU, BPS);                \
-    else REDB(false, false, UU, BPS);                        \
+    if (relu && dzb && qH) REDB(true, 2, UU, BPS);           \
+    else if (relu && dzb) REDB(true, 1, UU, BPS);            \
+    else if (relu) REDB(true, 0, UU, BPS);                   \
+    else if (dzb && qH) REDB(false, 2, UU, BPS);             \
+    else if (dzb) REDB(false, 1, UU, BPS);                   \
+    else REDB(false, 0, UU, BPS);                            \
   } while (0)
   // batched variants need the 1-bit ReLU mask (or no ReLU); the z-tensor form keeps the plain loop
-  const int variant = (relu && !mk) ? 0 : g_bn_reduce_variant;
+  if (qH && ((relu && !mk) || !dres)) return cudaErrorInvalidValue;   // compact second input: mask form + dres only
+  const int variant = (relu && !mk) ? 0 : ((qH && g_bn_reduce_variant == 0) ? 2 : g_bn_reduce_variant);
   if (given_blocks > 0) {
     nblk = given_blocks;
   } else if (variant == 0) {

@@ -148,6 +148,14 @@ int b2_bn_bwd(const void* dz_a, const void* dz_b, const void* z, const void* rel
               void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta,
               int accumulate, int relu, float* coef, float* partial, const b2_xgpu_ctx* xg, int xg_slot,
               void* stream);
+/* b2_bn_bwd with the second incoming gradient given at HALF resolution: dz_b_q [N, ceil(H/2), ceil(W/2), C] stands for
+ * the [N, H, W, C] tensor that equals it at the even pixels and is zero elsewhere - the input gradient of a 1x1 /
+ * stride 2 downsample convolution (torchvision's `downsample[0]`), which is then a plain GEMM on the half-resolution
+ * grid: no zero fill of the full tensor, a quarter of the bytes read here. relu_mask and dres are required. */
+int b2_bn_bwd_q(const void* dz_a, const void* dz_b_q, int H, int W, const void* relu_mask, const void* y, void* dy,
+                void* dres, long long M, int C, const float* gamma, const float* mean, const float* invstd,
+                float* dgamma, float* dbeta, int accumulate, int relu, float* coef, float* partial,
+                const b2_xgpu_ctx* xg, int xg_slot, void* stream);
 /* Same for a single incoming gradient whose reduce pass already happened: partial holds partial_blocks rows of
  * [2][C] written by b2_conv_dgrad_bnstats. */
 int b2_bn_bwd_partial(const void* dz, const void* z, const void* relu_mask, const void* y, void* dy, long long M,

@@ -277,6 +277,8 @@ class ResNetEngine:
         self.fuse_fanin = os.environ.get("B200DDP_FUSE_FANIN", "0") == "1"
         # the dgrad that produces a BatchNorm's output gradient also produces that BatchNorm's backward sums
         self.fuse_bn_bwd = os.environ.get("B200DDP_FUSE_BN_BWD", "1") != "0"
+        # strided 1x1 downsample: half-resolution input gradient, read compactly by the BatchNorm backward it feeds
+        self.compact_ds_grad = os.environ.get("B200DDP_COMPACT_DS_GRAD", "1") != "0"
         self._bn_blocks = 0
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
@@ -444,7 +446,7 @@ class ResNetEngine:
         return out
 
     def _unit_bwd(self, rec, dz_a, dz_b, need_dx, want_dres, grads, pre_masked=False, fan=None,
-                  given_blocks=0, next_rec=None):
+                  given_blocks=0, next_rec=None, dz_b_half_res=False, compact_dx=False):
         """Backward of one conv+BN(+ReLU) unit. ``pre_masked``: dz_a already is the complete, ReLU-masked gradient
         of this unit's output (produced by a fan-in dgrad), so it doubles as the residual-branch gradient.
         ``fan`` = (skip gradient, record of the previous block's last unit): fuse the residual fan-in, the ReLU
@@ -473,7 +475,8 @@ class ResNetEngine:
         else:
             dy, dres = native.bn_bwd(dz_a, dz_b, None, rec.y, bn.weight, st.mean, st.invstd,
                                      dg_slot[0], db_slot[0], dg_slot[1] and db_slot[1], rec.relu, st.coef, want_dres,
-                                     self._sync_bn_ctx(bn), self._next_xg_slot(bn), rec.mask)
+                                     self._sync_bn_ctx(bn), self._next_xg_slot(bn), rec.mask,
+                                     dz_b_half_res=dz_b_half_res)
         self._publish(bn.weight, dg_slot, grads)
         self._publish(bn.bias, db_slot, grads)
         w = conv.weight
@@ -502,6 +505,12 @@ class ResNetEngine:
             dx, self._bn_blocks = convops.conv_dgrad_bnstats(dy, self._w16(w), rec.x.shape, s, pd, next_rec.y,
                                                              next_rec.mask, nst.mean,
                                                              native.bn_partial_b(self.device))
+        if need_dx and dx is None and compact_dx:
+            # 1x1 / stride 2 (downsample): the input gradient is non-zero at the even pixels only - compute just those,
+            # as a plain GEMM on the half-resolution grid; the consumer (the previous block's BatchNorm backward)
+            # reads the compact tensor (native.bn_bwd dz_b_half_res) instead of a zero-filled full-size one
+            n_, c_ = rec.x.shape[0], rec.x.shape[1]
+            dx = convops.conv_dgrad(dy, self._w16(w), (n_, c_, dy.shape[2], dy.shape[3]), 1, 0)
         if need_dx and dx is None:
             dx = convops.conv_dgrad(dy, self._w16(w), rec.x.shape, s, pd)
         g = self._deliver(w, lambda out, acc: convops.conv_wgrad(rec.x, dy, w.shape, s, pd, out=out, accumulate=acc))
@@ -548,6 +557,7 @@ class ResNetEngine:
         da, db = native.avgpool_bwd(dpooled, feat_shape), None
         rev = list(reversed(block_tapes))
         pre_blocks = 0       # > 0: da is the finished fan-in gradient of the block output, sums are in bn_partial_b
+        db_half = False      # db is a compact half-resolution downsample gradient (see _unit_bwd compact_dx)
         for i, (blk, bt) in enumerate(rev):
             n_main = len(blk.units())
             recs_main = bt[:n_main - 1]
@@ -556,7 +566,8 @@ class ResNetEngine:
             # each dgrad of the main path also produces the BatchNorm-backward sums of the unit it feeds
             chain = list(recs_main)            # first .. last-but-one unit of the main path
             d, dres = self._unit_bwd(rec_last, da, db, True, True, grads, pre_masked=pre_blocks > 0,
-                                     given_blocks=pre_blocks, next_rec=chain[-1])
+                                     given_blocks=pre_blocks, next_rec=chain[-1], dz_b_half_res=db_half)
+            db_half = False
             blocks_first = self._bn_blocks
             for j in range(len(chain) - 1, 0, -1):
                 d, _ = self._unit_bwd(chain[j], d, None, True, False, grads, given_blocks=self._bn_blocks,
@@ -567,7 +578,14 @@ class ResNetEngine:
             # also produces the BatchNorm-backward sums of the previous block's last unit
             skip = dres
             if rec_ds is not None:
-                skip, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads)
+                # a strided 1x1 downsample hands its input gradient on in compact form when the consumer is another
+                # block's BatchNorm backward with a ReLU mask (always, except in front of the stem's max-pool)
+                compact = (self.compact_ds_grad and not self.fuse_fanin and rec_ds.conv.kernel_size == (1, 1)
+                           and rec_ds.conv.stride == (2, 2) and rec_ds.conv.padding == (0, 0) and i + 1 < len(rev)
+                           and rev[i + 1][1][-1].relu and rev[i + 1][1][-1].mask is not None
+                           and rec_ds.x.shape[2] % 2 == 0 and rec_ds.x.shape[3] % 2 == 0)
+                skip, _ = self._unit_bwd(rec_ds, dres, None, True, False, grads, compact_dx=compact)
+                db_half = compact
             prev_last = rev[i + 1][1][-1] if i + 1 < len(rev) else None
             pre_blocks = 0
             if self.fuse_fanin and prev_last is not None and prev_last.relu and prev_last.mask is not None:

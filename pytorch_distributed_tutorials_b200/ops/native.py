@@ -100,12 +100,23 @@ def bn_bwd_partial(dz, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, 
 
 
 def bn_bwd(dz_a, dz_b, z, y, gamma, mean, invstd, dgamma, dbeta, accumulate, relu, coef, want_dres, xg=None,
-           xg_slot=0, mask=None):
+           xg_slot=0, mask=None, dz_b_half_res=False):
     """aten::native_batch_norm_backward + threshold_backward + the gradient fan-in add, fused.
-    Returns (dy, dres) where dres (optional) is the masked incoming gradient for the residual branch."""
+    Returns (dy, dres) where dres (optional) is the masked incoming gradient for the residual branch.
+    ``dz_b_half_res``: dz_b is the compact [N, C, ceil(H/2), ceil(W/2)] input gradient of a 1x1 / stride 2
+    convolution (non-zero at the even pixels only)."""
     M, C = _mc(y)
     dy = torch.empty_like(y)
     dres = torch.empty_like(y) if want_dres else None
+    if dz_b_half_res:
+        assert mask is not None and want_dres
+        e = _lib.lib().b2_bn_bwd_q(ptr(dz_a), ptr(dz_b), int(y.shape[2]), int(y.shape[3]), ptr(mask), ptr(y), ptr(dy),
+                                   ptr(dres), c_ll(M), C, ptr(gamma), ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta),
+                                   int(accumulate), int(relu), ptr(coef), ptr(bn_partial(y.device)), _xg(xg), xg_slot,
+                                   stream_ptr())
+        check(e, "b2_bn_bwd_q")
+        count_launch(3)
+        return dy, dres
     e = _lib.lib().b2_bn_bwd(ptr(dz_a), ptr(dz_b), ptr(z), ptr(mask), ptr(y), ptr(dy), ptr(dres), c_ll(M), C, ptr(gamma),
                              ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta), int(accumulate), int(relu), ptr(coef),
                              ptr(bn_partial(y.device)), _xg(xg), xg_slot, stream_ptr())

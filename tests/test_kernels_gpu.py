@@ -121,6 +121,31 @@ def test_bn_forward_backward(C, H, N, relu, res):
         assert torch.equal(dy2, dy) and torch.equal(dres2, dres) and torch.equal(dg2, dgamma)
 
 
+@pytest.mark.parametrize("C,H,W,N", [(256, 56, 56, 4), (512, 28, 28, 3), (64, 8, 6, 5), (1024, 14, 14, 2)])
+def test_bn_backward_with_half_resolution_skip_gradient(C, H, W, N):
+    """The second incoming gradient given compactly at the even pixels (input gradient of a 1x1 / stride 2
+    downsample) must give exactly what the zero-filled full-resolution tensor gives."""
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(11)
+    y = _bf(torch.randn(N, C, H, W, device=DEV))
+    dza = _bf(torch.randn(N, C, H, W, device=DEV))
+    q = _bf(torch.randn(N, C, H // 2, W // 2, device=DEV))
+    full = torch.zeros(N, C, H, W, device=DEV)
+    full[:, :, ::2, ::2] = q.float()
+    full = _bf(full)
+    mask = torch.randint(0, 256, (y.numel() // 8,), device=DEV, dtype=torch.uint8)
+    gamma, mean, invstd = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV) * 0.1, torch.rand(C, device=DEV) + 0.5
+    outs = []
+    for dzb, half in ((full, False), (q, True)):
+        dg, db, coef = torch.empty(C, device=DEV), torch.empty(C, device=DEV), torch.empty(3 * C, device=DEV)
+        dy, dres = native.bn_bwd(dza, dzb, None, y, gamma, mean, invstd, dg, db, False, True, coef, True, mask=mask,
+                                 dz_b_half_res=half)
+        torch.cuda.synchronize()
+        outs.append((dy.clone(), dres.clone(), dg.clone(), db.clone()))
+    for a_, b_ in zip(*outs):
+        assert torch.equal(a_, b_)
+
+
 def test_bn_eval():
     from pytorch_distributed_tutorials_b200.ops import native
     C = 128

@@ -180,3 +180,39 @@ def test_train_entry_point_end_to_end_gloo(tmp_path):
     assert len(sd) == 122 and all(k.startswith("module.") for k in sd)
     r2 = subprocess.run(base + ["--resume"], env=env, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r2.returncode == 0, r2.stdout[-2000:] + r2.stderr[-4000:]
+
+
+def test_tail_bucket_split_keeps_order_and_sizes():
+    """The exposed-tail cut only re-labels the parameters at the END of the last bucket: order, totals and every
+    other bucket are untouched, and what is cut off is at most the requested size."""
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet50
+    from pytorch_distributed_tutorials_b200.parallel.ddp import split_tail_bucket
+    from pytorch_distributed_tutorials_b200.parallel.flat import plan_buckets
+    m = resnet50()
+    sizes = [p.numel() * 4 for p in m.grad_ready_order()]
+    plan = plan_buckets(sizes, 1 << 20, 25 << 20)
+    cut = split_tail_bucket(plan, sizes, 1 << 20)
+    cut2 = split_tail_bucket(cut, sizes, 1 << 16)
+    for a, b in ((plan, cut), (cut, cut2)):
+        assert len(a) == len(b) and max(b) == max(a) + 1
+        assert all(x <= y for x, y in zip(b, b[1:]))                      # still contiguous runs in ready order
+        last = max(a)
+        assert [x for x in b if x < last] == [x for x in a if x < last]   # earlier buckets untouched
+    tail_bytes = sum(s for s, k in zip(sizes, cut2) if k == max(cut2))
+    mid_bytes = sum(s for s, k in zip(sizes, cut2) if k == max(cut2) - 1)
+    assert 0 < tail_bytes <= 1 << 16 and 0 < mid_bytes <= 1 << 20
+    assert split_tail_bucket(plan, sizes, 0) == plan                       # switched off
+    assert split_tail_bucket([0, 0], [8, 8], 4) == [0, 0]                  # nothing small enough to cut off
+
+
+def test_device_prefetcher_ring_preserves_order_and_values_on_cpu():
+    """The prefetcher's ring / look-ahead bookkeeping (device side is plain tensors on CPU): every batch comes out
+    once, in order, including a ragged last batch that does not fit the ring's buffers."""
+    from pytorch_distributed_tutorials_b200.utils.data import DevicePrefetcher
+    batches = [(torch.full((4, 3), float(i)), torch.full((4,), i)) for i in range(7)] + \
+              [(torch.full((2, 3), 7.0), torch.full((2,), 7))]
+    for depth in (1, 2, 3):
+        out = [(x.clone(), y.clone()) for x, y in DevicePrefetcher(batches, "cpu", depth=depth)]
+        assert len(out) == 8
+        for i, (x, y) in enumerate(out):
+            assert x.shape[0] == (4 if i < 7 else 2) and bool((x == float(i)).all()) and bool((y == i).all())
