@@ -235,6 +235,62 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
   }
 }
 
+// Same pass, every thread owning one 8-channel vector (scale / shift in registers) and issuing the loads of U row
+// groups back to back; the grid-stride kernel above re-reads scale / shift from L1 for every 16 bytes and reaches only
+// ~58 % of the copy bandwidth on the narrow (64..512-channel) tensors.
+template <bool RELU, bool RES, int U, int BPS>
+__global__ void __launch_bounds__(kBnThreads, BPS)
+    bn_apply_batched_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res,
+                            const float* __restrict__ scale, const float* __restrict__ shift,
+                            __nv_bfloat16* __restrict__ z, unsigned char* __restrict__ mask, long long M, int C) {
+  const int C8 = C >> 3, RP = kBnThreads / C8;
+  const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
+  if (r >= RP) return;
+  const Vec8 sc = load_f32x8(scale + cv * 8), sh = load_f32x8(shift + cv * 8);
+  const long long step = (long long)gridDim.x * RP;
+  for (long long row0 = (long long)blockIdx.x * RP + r; row0 < M; row0 += step * U) {
+    uint4 uy[U], ur[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * step;
+      if (row < M) {
+        const long long off = row * C + cv * 8;
+        uy[u] = ld_nc_v4(y + off);
+        if (RES) ur[u] = ld_nc_v4(res + off);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * step;
+      if (row < M) {
+        const long long off = row * C + cv * 8;
+        const uint32_t yw[4] = {uy[u].x, uy[u].y, uy[u].z, uy[u].w};
+        uint32_t ow[4];
+        unsigned bits = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float o0 = fmaf(__uint_as_float(yw[q] << 16), sc.v[2 * q], sh.v[2 * q]);
+          float o1 = fmaf(__uint_as_float(yw[q] & 0xffff0000u), sc.v[2 * q + 1], sh.v[2 * q + 1]);
+          if (RES) {
+            const uint32_t rw = q == 0 ? ur[u].x : (q == 1 ? ur[u].y : (q == 2 ? ur[u].z : ur[u].w));
+            o0 += __uint_as_float(rw << 16);
+            o1 += __uint_as_float(rw & 0xffff0000u);
+          }
+          if (RELU) {
+            bits |= (o0 > 0.f ? 1u : 0u) << (2 * q);
+            bits |= (o1 > 0.f ? 1u : 0u) << (2 * q + 1);
+            o0 = fmaxf(o0, 0.f);
+            o1 = fmaxf(o1, 0.f);
+          }
+          ow[q] = pack_bf16x2(o0, o1);
+        }
+        if (RELU && mask) mask[off >> 3] = (unsigned char)bits;
+        *reinterpret_cast<uint4*>(z + off) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ backward
 // dz' = (dz_a [+ dz_b]) * (z > 0 if RELU).  Accumulates sum(dz') and sum(dz' * (y - mean)) per channel.
 // GOUT: dz' (rounded to bf16, which is what the sums then use) is also written out - it is the gradient of the
@@ -491,6 +547,58 @@ __global__ void __launch_bounds__(256)
 // Default 2: measured on B200 (tools/bn_bench.py, batch 256, reduce + apply of a residual block output):
 // C=256 @56x56 0.546 ms (variant 0) / 0.535 (1) / 0.475 (2) / 0.497 (3); every ResNet-50 shape ranks the same way.
 static int g_bn_reduce_variant = 2;
+static int g_bn_apply_batched = 1;   // b2_bn_set_apply_batched(0): grid-stride apply kernels again
+
+// dy = k1*g + k2*y + k3 with g = dz (optionally masked by the 1-bit ReLU mask): the apply pass in the shape of the
+// batched reduce pass - every thread owns one 8-channel vector for the whole kernel (the three coefficient vectors
+// live in registers instead of being re-read from L1 for every 16 bytes of data) and issues the loads of U row groups
+// back to back. The grid-stride version above reaches 80 % of the copy bandwidth on the wide tensors.
+template <bool RELU, int U, int BPS>
+__global__ void __launch_bounds__(kBnThreads, BPS)
+    bn_bwd_apply_batched_kernel(const __nv_bfloat16* __restrict__ dz, const unsigned char* __restrict__ mask,
+                                const __nv_bfloat16* __restrict__ y, const float* __restrict__ coef,
+                                __nv_bfloat16* __restrict__ dy, long long M, int C) {
+  const int C8 = C >> 3, RP = kBnThreads / C8;
+  const int cv = threadIdx.x % C8, r = threadIdx.x / C8;
+  if (r >= RP) return;
+  const Vec8 k1 = load_f32x8(coef + cv * 8), k2 = load_f32x8(coef + C + cv * 8), k3 = load_f32x8(coef + 2 * C + cv * 8);
+  const long long step = (long long)gridDim.x * RP;
+  for (long long row0 = (long long)blockIdx.x * RP + r; row0 < M; row0 += step * U) {
+    uint4 ug[U], uy[U];
+    unsigned bits[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * step;
+      if (row < M) {
+        const long long off = row * C + cv * 8;
+        ug[u] = ld_nc_v4(dz + off);
+        uy[u] = ld_nc_v4(y + off);
+        if (RELU) bits[u] = mask[off >> 3];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * step;
+      if (row < M) {
+        const uint32_t gw[4] = {ug[u].x, ug[u].y, ug[u].z, ug[u].w};
+        const uint32_t yw[4] = {uy[u].x, uy[u].y, uy[u].z, uy[u].w};
+        uint32_t ow[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float g0 = __uint_as_float(gw[q] << 16), g1 = __uint_as_float(gw[q] & 0xffff0000u);
+          if (RELU) {
+            g0 = ((bits[u] >> (2 * q)) & 1u) ? g0 : 0.f;
+            g1 = ((bits[u] >> (2 * q + 1)) & 1u) ? g1 : 0.f;
+          }
+          const float y0 = __uint_as_float(yw[q] << 16), y1 = __uint_as_float(yw[q] & 0xffff0000u);
+          ow[q] = pack_bf16x2(fmaf(k1.v[2 * q], g0, fmaf(k2.v[2 * q], y0, k3.v[2 * q])),
+                              fmaf(k1.v[2 * q + 1], g1, fmaf(k2.v[2 * q + 1], y1, k3.v[2 * q + 1])));
+        }
+        *reinterpret_cast<uint4*>(dy + row * C + cv * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
+  }
+}
 
 static int plan_blocks(long long M, int C, long long* rows_per_blk) {
   const int C8 = C / 8, RP = kBnThreads / C8;
@@ -518,6 +626,7 @@ using namespace b2;
 
 B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_bn)
 
+extern "C" void b2_bn_set_apply_batched(int on) { g_bn_apply_batched = on; }
 extern "C" void b2_bn_set_reduce_variant(int v) { g_bn_reduce_variant = (v >= 0 && v <= 3) ? v : 0; }
 extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartialBlocks * 2 * C; }
 
@@ -550,6 +659,17 @@ static int bn_fwd_train_impl(const void* y, const void* res, void* z, void* relu
   const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
   __nv_bfloat16* zz = (__nv_bfloat16*)z;
   unsigned char* mk = (unsigned char*)relu_mask;
+  if (g_bn_apply_batched && bn_shape_ok(C)) {
+    const int RPa = kBnThreads / (C / 8);
+    long long gb = (long long)host_num_sms() * 2, need = (M + RPa - 1) / RPa;
+    if (gb > need) gb = need < 1 ? 1 : need;
+    const float *scp = scale_shift, *shp = scale_shift + C;
+    if (relu && res) bn_apply_batched_kernel<true, true, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else if (relu) bn_apply_batched_kernel<true, false, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else if (res) bn_apply_batched_kernel<false, true, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else bn_apply_batched_kernel<false, false, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    return cudaGetLastError();
+  }
   if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
@@ -589,6 +709,17 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
   const __nv_bfloat16* rr = (const __nv_bfloat16*)res;
   __nv_bfloat16* zz = (__nv_bfloat16*)z;
   unsigned char* mk = nullptr;
+  if (g_bn_apply_batched && bn_shape_ok(C)) {
+    const int RPa = kBnThreads / (C / 8);
+    long long gb = (long long)host_num_sms() * 2, need = (M + RPa - 1) / RPa;
+    if (gb > need) gb = need < 1 ? 1 : need;
+    const float *scp = scale_shift, *shp = scale_shift + C;
+    if (relu && res) bn_apply_batched_kernel<true, true, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else if (relu) bn_apply_batched_kernel<true, false, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else if (res) bn_apply_batched_kernel<false, true, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    else bn_apply_batched_kernel<false, false, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(yy, rr, scp, shp, zz, mk, M, C);
+    return cudaGetLastError();
+  }
   if (relu && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   else if (relu) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
   else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(yy, rr, scale_shift, scale_shift + C, zz, mk, nvec, C / 8);
@@ -701,6 +832,18 @@ static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const 
                                                           dbeta, accumulate, coef, ctx, xg_slot);
   const long long nvec = M * (C / 8);
   const int grid = stream_grid(nvec);
+  // batched apply (one incoming gradient, mask form or no ReLU): same grid rule as the batched reduce pass
+  const bool batched_apply = g_bn_apply_batched && (dres || (!dzb && (!relu || mk)));
+  if (batched_apply) {
+    long long gb = (long long)host_num_sms() * 2;
+    long long need = (M + RP - 1) / RP;
+    if (gb > need) gb = need < 1 ? 1 : need;
+    if (dres || !relu)
+      bn_bwd_apply_batched_kernel<false, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(dres ? drp : a, nullptr, yy, coef, dyp, M, C);
+    else
+      bn_bwd_apply_batched_kernel<true, 4, 2><<<(int)gb, kBnThreads, 0, st>>>(a, mk, yy, coef, dyp, M, C);
+    return cudaGetLastError();
+  }
   if (dres) {
     // the reduce pass has already produced dz' (= dres): dy = k1*dres + k2*y + k3
     bn_bwd_apply_kernel<false, false, false><<<grid, 256, 0, st>>>(drp, nullptr, nullptr, nullptr, yy, coef, dyp,

@@ -110,6 +110,8 @@ long long b2_bn_partial_floats(int C);
 /* Tuning: load batching of the backward reduce pass. 0 = plain unrolled loop, 1 = 2 row groups of loads issued back
  * to back @ 4 CTAs/SM, 2 = 4 groups @ 2 CTAs/SM, 3 = 3 groups @ 3 CTAs/SM. */
 void b2_bn_set_reduce_variant(int v);
+/* 1 (default): backward apply pass with per-thread channel ownership and batched loads; 0: grid-stride kernels. */
+void b2_bn_set_apply_batched(int on);
 /* relu_mask (optional, u8 [M*C/8]): one bit per output element, set where the ReLU passed; the backward pass can
  * then be given the mask instead of z (16x fewer bytes). */
 int b2_bn_fwd_train(const void* y, const void* res, void* z, void* relu_mask, long long M, int C,

@@ -56,6 +56,13 @@ def lib():
             if not ok:
                 raise NativeError("libb200ddp.so not found at %s — run `python build.py`" % LIB_PATH)
         _lib = ctypes.CDLL(LIB_PATH)
+        # tuning switches of the kernel library that have an environment spelling (A/B runs without code changes)
+        for env, setter in (("B200DDP_BN_APPLY_BATCHED", "b2_bn_set_apply_batched"),
+                            ("B200DDP_BN_REDUCE_VARIANT", "b2_bn_set_reduce_variant"),
+                            ("B200DDP_CONV_HALO", "b2_conv_set_halo")):
+            v = os.environ.get(env)
+            if v is not None and hasattr(_lib, setter):
+                getattr(_lib, setter)(int(v))
         return _lib
 
 
