@@ -398,8 +398,18 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
   long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4;
   if (i >= n) return;
   float4 acc = accumulate ? *reinterpret_cast<const float4*>(dw + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int s = 0; s < splits; ++s) {
-    float4 v = *reinterpret_cast<const float4*>(ws + s * split_stride + i);
+  // eight partial slabs requested at a time, added in slab order (the sum stays bit-reproducible): with one load in
+  // flight per thread the kernel was pure latency (up to 148 dependent round trips for the small weight tensors)
+  int s = 0;
+  for (; s + 8 <= splits; s += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcs(reinterpret_cast<const float4*>(ws + (long long)(s + u) * split_stride + i));
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+  }
+  for (; s < splits; ++s) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(ws + (long long)s * split_stride + i));
     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
   }
   *reinterpret_cast<float4*>(dw + i) = acc;

@@ -41,20 +41,30 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
     unsigned arg[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
+    // all nine taps are requested before the first comparison (clamped addresses, validity applied afterwards): nine
+    // independent 16-byte loads in flight per thread instead of a load behind every branch
+    uint4 raw[9];
+    bool ok[9];
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
       const int h = oh * 2 - 1 + kh;
-      if (h < 0 || h >= H) continue;
+      const int hc = h < 0 ? 0 : (h >= H ? H - 1 : h);
 #pragma unroll
       for (int kw = 0; kw < 3; ++kw) {
         const int w = ow * 2 - 1 + kw;
-        if (w < 0 || w >= W) continue;
-        float v[8];
-        unpack8(*reinterpret_cast<const uint4*>(x + (((long long)(n * H + h) * W + w) * C8 + cv) * 8), v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (v[j] > m[j] || arg[j] == 255u) { m[j] = v[j]; arg[j] = kh * 3 + kw; }
+        const int wc = w < 0 ? 0 : (w >= W ? W - 1 : w);
+        ok[kh * 3 + kw] = (h == hc) && (w == wc);
+        raw[kh * 3 + kw] = ld_nc_v4(x + (((long long)(n * H + hc) * W + wc) * C8 + cv) * 8);
       }
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      if (!ok[t]) continue;
+      float v[8];
+      unpack8(raw[t], v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (v[j] > m[j] || arg[j] == 255u) { m[j] = v[j]; arg[j] = t; }
     }
     *reinterpret_cast<uint4*>(y + i * 8) = pack8(m);
     if (idx) {
