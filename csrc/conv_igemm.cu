@@ -63,6 +63,10 @@ struct ConvParams {
   const unsigned char* amask;   // [M][Ncols/8] bits, optional (only with add)
   int panels;  // v2, MN-major operands fetched as one multi-panel TMA box: bit 0 = A (wgrad), bit 1 = B (dgrad/wgrad)
   int dbg;  // timing experiments only (b2_conv_set_debug): 1 = skip the TMA loads once the ring is primed, 2 = skip the MMAs
+  // wgrad (v2): 0 = every split stores its fp32 slab (wgrad_reduce_kernel sums them in a fixed order afterwards);
+  // 1 = `out` is dW itself and every split adds its tile with red.global.add.v4.f32 (the sum forms in L2, no slab
+  // round trip, no second kernel; the order of the fp32 additions is whatever the memory system makes it).
+  int red_out;
 };
 
 constexpr int BM = 128;
@@ -450,6 +454,7 @@ static int g_force_bn = 0;
 static int g_dbg = 0;
 static int g_mt2 = 1;     // v2 wgrad: 256 x 256 tile per CTA where Cout allows (b2_conv_set_wgrad_mt2)
 static int g_wgrad_waves = 1;   // v2 wgrad split-K target: work items per SM (1: half the partial-sum traffic of 2)
+static int g_wgrad_red = 1;  // v2 wgrad: split-K sums form in L2 (red.add.v4.f32 into dW) instead of slabs + a reduce kernel
 static int g_panels = 1;  // v2: fetch MN-major operands as one multi-panel TMA box (b2_conv_set_panels)
 static int g_act_mode = -1;  // -1 auto, else force ACT_GATHER / ACT_IM2COL for k>1 or strided convs
 
@@ -1129,6 +1134,7 @@ __global__ void __launch_bounds__(KIND == WGRAD ? kThreads2W : kThreads2 + 32 * 
         }
       } else {
         float* out = reinterpret_cast<float*>(p.out) + (size_t)it.split * p.split_stride;
+        const bool red = p.red_out != 0;
 #pragma unroll 1
         for (int mt = 0; mt < MT; ++mt) {
           const int mm = m + mt * BM;
@@ -1141,8 +1147,12 @@ __global__ void __launch_bounds__(KIND == WGRAD ? kThreads2W : kThreads2 + 32 * 
             if (mm < p.M) {
 #pragma unroll
               for (int q = 0; q < 8; ++q)
-                if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols)
-                  st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+                if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols) {
+                  if (red)
+                    red_add_v4(orow + c * 32 + q * 4, v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                  else
+                    st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+                }
             }
           }
         }
@@ -1529,6 +1539,7 @@ extern "C" void b2_conv_set_debug(int bits) { g_dbg = bits; }
 extern "C" void b2_conv_set_panels(int on) { g_panels = on; }
 extern "C" void b2_conv_set_wgrad_mt2(int on) { g_mt2 = on; }
 extern "C" void b2_conv_set_wgrad_waves(int n) { g_wgrad_waves = n; }
+extern "C" void b2_conv_set_wgrad_red(int on) { g_wgrad_red = on; }
 
 extern "C" void b2_conv_set_impl(int impl) { g_impl = impl; }
 
@@ -1820,6 +1831,8 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
                              int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int accumulate,
                              void* stream) {
   if (Cin % 64 || Cout % 8) return cudaErrorInvalidValue;
+  const bool fixed_order = (accumulate & 2) != 0;   // caller asks for run-to-run identical sums
+  accumulate &= 1;
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   const int taps = KH * KW;
   const long long kpix = (long long)N * Ho * Wo;
@@ -1862,6 +1875,17 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t ce;
   const bool pairs = use_pairs(bn, Cout) && Cout % 256 == 0 && mode != ACT_GATHER && (flat || taps == 1);
+  // Split-K sums formed in L2 by the epilogue's vector reductions, straight into dW: the persistent kernel only.
+  // A single split that overwrites needs neither the reductions nor the slab.
+  const bool direct = g_wgrad_red && !fixed_order && !pairs && (flat || (g_impl >= 2 && mode != ACT_GATHER));
+  if (direct) {
+    p.out = dw; p.split_stride = 0;
+    p.red_out = (splits > 1 || accumulate) ? 1 : 0;
+    if (p.red_out && !accumulate) {
+      ce = cudaMemsetAsync(dw, 0, (size_t)wcount * 4, st);
+      if (ce != cudaSuccess) return ce;
+    }
+  }
   if (pairs) {   // 256 rows of Cout per CTA pair; N is the flattened (tap, cin) axis
     p.flatN = 1;
     p.Ncols = taps * Cin;
@@ -1892,6 +1916,7 @@ extern "C" int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* wo
     ce = launch_mode<WGRAD>(mode, bn, tmA, tmB, p, grid, st);
   }
   if (ce != cudaSuccess) return ce;
+  if (direct) return cudaSuccess;
   const int thr = 256;
   const long long nvec = (wcount + 3) / 4;
   wgrad_reduce_kernel<<<(unsigned)((nvec + thr - 1) / thr), thr, 0, st>>>(workspace, dw, wcount, splits, wcount,

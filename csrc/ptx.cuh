@@ -391,5 +391,12 @@ B2_DEVICE void st_v4(void* p, uint4 v) {
   asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
+// Four fp32 additions into global memory in one 16-byte reduction (performed by the L2; no value returned). The
+// operands are the raw bits of the floats, as they come out of tcgen05.ld.
+B2_DEVICE void red_add_v4(float* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__uint_as_float(a)),
+               "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
+               : "memory");
+}
 
 }  // namespace b2

@@ -55,6 +55,10 @@ void b2_conv_set_panels(int on);
 void b2_conv_set_wgrad_mt2(int on);
 /* split-K target of the 128-row wgrad tiles: work items per SM (1 = default: fewer, longer splits; 2) */
 void b2_conv_set_wgrad_waves(int n);
+/* 1 (default): the split-K sums of wgrad form in L2 - every split adds its tile into dw with 16-byte fp32 reductions,
+ * no slab round trip through the workspace and no second kernel; the order of those additions is not fixed, so two
+ * runs can differ in the last bits. 0: slabs + a fixed-order reduce kernel everywhere (run-to-run identical). */
+void b2_conv_set_wgrad_red(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* dgrad that also produces the partial sums of the BatchNorm backward whose output gradient it computes (statistics
@@ -73,7 +77,8 @@ int b2_conv_dgrad_fused(const void* dy, const void* w, void* dx, int N, int H, i
                         int KW, int stride, int pad, const void* add, const void* mask, const void* bn_y,
                         const float* bn_mean, float* partial, int* blocks, void* stream);
 /* workspace: fp32 scratch for split-K partials, at least Cout*KH*KW*Cin*4 bytes; larger lets more SMs work.
- * accumulate != 0 adds into dw (gradient accumulation / no_sync), otherwise dw is overwritten. */
+ * accumulate bit 0: add into dw (gradient accumulation / no_sync), otherwise dw is overwritten.
+ * accumulate bit 1: this call must sum its splits in a fixed order (see b2_conv_set_wgrad_red). */
 int b2_conv_wgrad(const void* x, const void* dy, float* dw, float* workspace, long long ws_bytes, int N, int H, int W,
                   int Cin, int Cout, int KH, int KW, int stride, int pad, int accumulate, void* stream);
 int b2_conv_wgrad_splits(int N, int Ho, int Wo, int Cin, int Cout, int taps, long long ws_bytes);

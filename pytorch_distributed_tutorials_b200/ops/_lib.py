@@ -59,7 +59,8 @@ def lib():
         # tuning switches of the kernel library that have an environment spelling (A/B runs without code changes)
         for env, setter in (("B200DDP_BN_APPLY_BATCHED", "b2_bn_set_apply_batched"),
                             ("B200DDP_BN_REDUCE_VARIANT", "b2_bn_set_reduce_variant"),
-                            ("B200DDP_CONV_HALO", "b2_conv_set_halo")):
+                            ("B200DDP_CONV_HALO", "b2_conv_set_halo"),
+                            ("B200DDP_WGRAD_RED", "b2_conv_set_wgrad_red")):
             v = os.environ.get(env)
             if v is not None and hasattr(_lib, setter):
                 getattr(_lib, setter)(int(v))

@@ -5,6 +5,7 @@ torchvision's ResNet (reference resnet/main.py:76,121,123).  Activations are bf1
 ``channels_last``), weights bf16 OHWI (``channels_last`` of the OIHW parameter), weight gradients fp32 OHWI.
 """
 import ctypes
+import os
 
 import torch
 import torch.nn.functional as F
@@ -13,6 +14,7 @@ from . import _lib
 
 _WS = {}
 _WS_BYTES = 256 << 20
+_WGRAD_RED = os.environ.get("B200DDP_WGRAD_RED", "1") != "0"
 
 
 def workspace(device):
@@ -62,15 +64,25 @@ def gemm_nn(dy, w):
     return dx
 
 
+def _wgrad_flags(accumulate):
+    """(flags for b2_conv_wgrad, launches it makes). Split-K sums normally form in L2 (fp32 reductions straight into
+    the gradient, order not fixed: the last bits can differ from run to run, as with cuDNN's default wgrad).
+    ``torch.use_deterministic_algorithms(True)`` or ``B200DDP_WGRAD_RED=0`` selects fp32 slabs + a fixed-order reduce
+    kernel instead."""
+    fixed_order = torch.are_deterministic_algorithms_enabled() or not _WGRAD_RED
+    return int(bool(accumulate)) | (2 if fixed_order else 0), (2 if fixed_order else 1)
+
+
 def gemm_tn(dy, a, out, accumulate=False):
     """out[N,K] fp32 (+)= dy[M,N]^T @ a[M,K] on the wgrad kernel (split-K over M). K % 64 == 0, N % 8 == 0."""
     M, N = dy.shape
     K = a.shape[1]
     ws = workspace(a.device)
+    flags, nlaunch = _wgrad_flags(accumulate)
     e = _lib.lib().b2_conv_wgrad(_lib.ptr(a), _lib.ptr(dy), _lib.ptr(out), _lib.ptr(ws), _lib.c_ll(ws.numel() * 4),
-                                 M, 1, 1, K, N, 1, 1, 1, 0, int(accumulate), _lib.stream_ptr())
+                                 M, 1, 1, K, N, 1, 1, 1, 0, flags, _lib.stream_ptr())
     _lib.check(e, "b2_conv_wgrad(gemm_tn)")
-    _lib.count_launch(2)
+    _lib.count_launch(nlaunch)
     return out
 
 
@@ -176,11 +188,12 @@ def conv_wgrad(x, dy, w_shape, stride, pad, out=None, accumulate=False):
             memory_format=torch.channels_last)
         accumulate = False
     ws = workspace(x.device)
+    flags, nlaunch = _wgrad_flags(accumulate)
     e = _lib.lib().b2_conv_wgrad(_lib.ptr(x), _lib.ptr(dy), _lib.ptr(out), _lib.ptr(ws),
                                  _lib.c_ll(ws.numel() * 4), N, H, W, Cin, Cout, KH, KW, stride, pad,
-                                 int(accumulate), _lib.stream_ptr())
+                                 flags, _lib.stream_ptr())
     _lib.check(e, "b2_conv_wgrad")
-    _lib.count_launch(2)
+    _lib.count_launch(nlaunch)
     return out
 
 

@@ -10,6 +10,15 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
+@pytest.fixture
+def fixed_order_sums():
+    """The bit-for-bit tests run with torch's determinism switch on: wgrad then sums its split-K slabs in a fixed order
+    (by default the sums form in L2 and their last bits vary from run to run, like cuDNN's default wgrad)."""
+    torch.use_deterministic_algorithms(True, warn_only=True)
+    yield
+    torch.use_deterministic_algorithms(False)
+
+
 def _cos(a, b):
     return torch.nn.functional.cosine_similarity(a.float().flatten(), b.float().flatten(), dim=0).item()
 
@@ -125,7 +134,7 @@ def test_eval_mode_with_grad_uses_running_statistics_in_backward():
     assert torch.allclose(m.layer1[0].bn1.weight.grad, ref.layer1[0].bn1.weight.grad, rtol=1e-3, atol=1e-5)
 
 
-def test_learning_rate_schedule_does_not_recapture_the_graph():
+def test_learning_rate_schedule_does_not_recapture_the_graph(fixed_order_sums):
     """The native SGD kernels read lr / momentum / weight decay from a device block: changing the learning rate
     every step keeps ONE captured graph, and the weights equal an eager run with the same schedule bit for bit."""
     from pytorch_distributed_tutorials_b200 import optim
@@ -218,7 +227,7 @@ def test_native_library_is_loaded():
     assert "libb200ddp.so" in maps
 
 
-def test_graphed_train_step_matches_eager():
+def test_graphed_train_step_matches_eager(fixed_order_sums):
     """Whole-step CUDA graph replay must follow the same trajectory as launching the kernels from Python."""
     from pytorch_distributed_tutorials_b200 import optim
     from pytorch_distributed_tutorials_b200.models.resnet import resnet18
@@ -248,7 +257,7 @@ def test_graphed_train_step_matches_eager():
     assert all(torch.equal(a, b) for a, b in zip(p_g, p_e))       # deterministic kernels: bit-identical weights
 
 
-def test_fused_reduce_update_equals_update_in_step():
+def test_fused_reduce_update_equals_update_in_step(fixed_order_sums):
     """Applying SGD as the epilogue of each bucket's reduction (during backward) must give exactly the weights that
     running the same update inside optimizer.step() gives: no kernel may read a weight after its bucket was updated."""
     from pytorch_distributed_tutorials_b200 import optim
@@ -299,3 +308,31 @@ def test_engine_delivers_gradients_in_the_planned_order(name):
     m(x).sum().backward()
     planned = [id(p) for p in m.grad_ready_order()]
     assert seen == planned
+
+
+def test_default_wgrad_sums_in_l2_and_stays_within_rounding_of_the_fixed_order_path():
+    """Default: every split adds its tile into dW with fp32 reductions in L2 (one launch fewer per layer, no slabs).
+    Against the fixed-order path the difference is fp32 rounding only; with the determinism switch two runs agree
+    bit for bit."""
+    from pytorch_distributed_tutorials_b200.ops import _lib, conv
+    torch.manual_seed(11)
+    for (n, h, ci, co, k, s, p) in ((32, 14, 256, 256, 3, 1, 1), (32, 28, 128, 512, 1, 1, 0), (32, 56, 64, 64, 3, 1, 1),
+                                    (16, 28, 256, 512, 1, 2, 0)):
+        x = torch.randn(n, ci, h, h, device=DEV).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        ho = (h + 2 * p - k) // s + 1
+        dy = torch.randn(n, co, ho, ho, device=DEV).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        l0 = _lib.launches()
+        fast = conv.conv_wgrad(x, dy, (co, ci, k, k), s, p)
+        assert _lib.launches() - l0 == 1
+        acc = fast.clone()
+        conv.conv_wgrad(x, dy, (co, ci, k, k), s, p, out=acc, accumulate=True)
+        torch.use_deterministic_algorithms(True, warn_only=True)
+        try:
+            a = conv.conv_wgrad(x, dy, (co, ci, k, k), s, p)
+            b = conv.conv_wgrad(x, dy, (co, ci, k, k), s, p)
+        finally:
+            torch.use_deterministic_algorithms(False)
+        assert torch.equal(a, b)
+        scale = a.abs().max().item()
+        assert (fast - a).abs().max().item() <= 2e-5 * scale
+        assert (acc - 2 * a).abs().max().item() <= 4e-5 * scale

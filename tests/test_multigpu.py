@@ -298,6 +298,7 @@ def _graph_ddp(rank, world):
     from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
     from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
     from pytorch_distributed_tutorials_b200.utils.graph import GraphedTrainStep
+    torch.use_deterministic_algorithms(True, warn_only=True)   # graph == eager bit for bit needs fixed-order wgrad sums
     dev = torch.device("cuda", rank)
     torch.manual_seed(0)
     base = resnet18().to(dev)
