@@ -1133,27 +1133,39 @@ __global__ void __launch_bounds__(KIND == WGRAD ? kThreads2W : kThreads2 + 32 * 
           }
         }
       } else {
+        // fp32 tile -> dW (or a split-K slab). Straight from the registers every warp instruction would touch 32
+        // rows with 16 bytes each (measured: half the store rate, tools/red_probe.cu), so each 32 x 32 block is
+        // transposed through a per-warp staging buffer (row pitch 144 B: conflict-free both ways) and leaves as
+        // 4 rows x 128 contiguous bytes per instruction.
         float* out = reinterpret_cast<float*>(p.out) + (size_t)it.split * p.split_stride;
         const bool red = p.red_out != 0;
+        uint8_t* stage = epi_smem + quad * (32 * 144);
+        const int rsub = lane >> 3, piece = lane & 7;
 #pragma unroll 1
         for (int mt = 0; mt < MT; ++mt) {
-          const int mm = m + mt * BM;
-          float* orow = out + (size_t)mm * p.out_ld + (size_t)it.tap * p.tapC + it.n0;
+          const int mm0 = it.m0 + mt * BM + quad * 32;   // first of this warp's 32 rows
+          float* obase = out + (size_t)(mm0 + rsub) * p.out_ld + (size_t)it.tap * p.tapC + it.n0 + piece * 4;
 #pragma unroll 1
           for (int c = 0; c < BN / 32; ++c) {
             uint32_t v[32];
             tmem_ld32(taddr + mt * BN + c * 32, v);
             tmem_ld_wait();
-            if (mm < p.M) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q)
-                if (!p.flatN || it.n0 + c * 32 + q * 4 + 4 <= p.Ncols) {
-                  if (red)
-                    red_add_v4(orow + c * 32 + q * 4, v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-                  else
-                    st_v4(orow + c * 32 + q * 4, make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
-                }
+            for (int q = 0; q < 8; ++q)
+              *reinterpret_cast<uint4*>(stage + lane * 144 + q * 16) =
+                  make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            __syncwarp();
+            const bool col_ok = !p.flatN || it.n0 + c * 32 + piece * 4 + 4 <= p.Ncols;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint4 o = *reinterpret_cast<const uint4*>(stage + (4 * j + rsub) * 144 + piece * 16);
+              if (col_ok && mm0 + 4 * j + rsub < p.M) {
+                float* dst = obase + (size_t)(4 * j) * p.out_ld + c * 32;
+                if (red) red_add_v4(dst, o.x, o.y, o.z, o.w);
+                else st_v4(dst, o);
+              }
             }
+            __syncwarp();
           }
         }
       }

@@ -36,6 +36,30 @@ __global__ void __launch_bounds__(128) epi_kernel(float* out, int tiles, int spl
   }
 }
 
+// Same bytes, but a warp instruction covers RPW rows x (512 / RPW) contiguous bytes (RPW = 32 is the row-per-thread
+// pattern above, RPW = 1 one 512-byte run): what a transposing epilogue would issue.
+template <int MODE, int RPW>
+__global__ void __launch_bounds__(128) epi_coal_kernel(float* out, int tiles, int splits, long long ld, long long slab) {
+  const int item = blockIdx.x;
+  if (item >= tiles * splits) return;
+  const int tile = item / splits, split = item % splits;
+  float* base = out + (MODE == 0 ? (long long)split * slab : 0) + (long long)tile * kCols;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  constexpr int LPR = 32 / RPW;          // lanes per row
+  constexpr int CPI = LPR * 4;           // columns per instruction and row
+  const int r_in = lane / LPR, piece = lane % LPR;
+  // warp w owns rows [w * 64, w * 64 + 64) of the 256-row tile
+  for (int r0 = 0; r0 < 64; r0 += RPW) {
+    float* row = base + (long long)(warp * 64 + r0 + r_in) * ld;
+#pragma unroll 4
+    for (int c = 0; c < kCols; c += CPI) {
+      const float4 v = make_float4(1.f, 2.f, 3.f, (float)split);
+      if (MODE == 0) *reinterpret_cast<float4*>(row + c + piece * 4) = v;
+      else red_v4(row + c + piece * 4, v);
+    }
+  }
+}
+
 // mode 2: the tile goes through shared memory (row-major 256 x 32 column chunks) and one thread per row issues a bulk
 // reduce of 128 bytes; measures the TMA reduction path with the same addresses
 __global__ void __launch_bounds__(128) epi_bulk_kernel(float* out, int tiles, int splits, long long ld) {
@@ -110,6 +134,31 @@ int main() {
         CK(cudaEventElapsedTime(&ms, e0, e1));
         if (r >= 0) t[mode] += ms;
       }
+    }
+    {
+      float tc[6] = {0, 0, 0, 0, 0, 0};
+      for (int mode = 0; mode < 6; ++mode)
+        for (int r = -3; r < reps; ++r) {
+          CK(cudaMemsetAsync(flush, r & 1, 256 << 20));
+          if (mode >= 3) CK(cudaMemsetAsync(dw, 0, slab * 4));
+          CK(cudaEventRecord(e0));
+          switch (mode) {
+            case 0: epi_coal_kernel<0, 1><<<items, 128>>>(ws, c.tiles, c.splits, ld, slab); break;
+            case 1: epi_coal_kernel<0, 4><<<items, 128>>>(ws, c.tiles, c.splits, ld, slab); break;
+            case 2: epi_coal_kernel<0, 32><<<items, 128>>>(ws, c.tiles, c.splits, ld, slab); break;
+            case 3: epi_coal_kernel<1, 1><<<items, 128>>>(dw, c.tiles, c.splits, ld, slab); break;
+            case 4: epi_coal_kernel<1, 4><<<items, 128>>>(dw, c.tiles, c.splits, ld, slab); break;
+            case 5: epi_coal_kernel<1, 32><<<items, 128>>>(dw, c.tiles, c.splits, ld, slab); break;
+          }
+          CK(cudaEventRecord(e1));
+          CK(cudaEventSynchronize(e1));
+          float ms;
+          CK(cudaEventElapsedTime(&ms, e0, e1));
+          if (r >= 0) tc[mode] += ms;
+        }
+      printf("   kernel alone, warp instruction = 1 / 4 / 32 rows: stores %6.2f %6.2f %6.2f us | red.v4 %6.2f %6.2f %6.2f us\n",
+             tc[0] / reps * 1e3, tc[1] / reps * 1e3, tc[2] / reps * 1e3, tc[3] / reps * 1e3, tc[4] / reps * 1e3,
+             tc[5] / reps * 1e3);
     }
     // check the red result: every element of the first row = sum over splits of (1,2,3,split)
     float h[4];

@@ -1,0 +1,67 @@
+"""Per-shape sweep of the N-tile width of the persistent implicit-GEMM kernel (b2_conv_set_tile_n): for every ResNet-50
+shape and op, time the default choice and each forced width as a captured graph of back-to-back launches.
+    python tools/tile_sweep.py --batch 256 [--shapes 7,14] [--ops fprop,dgrad,wgrad] [--out profiles/tile_sweep.md]
+Used to decide where wave quantisation (items % SMs) makes a narrower tile pay."""
+import argparse
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from pytorch_distributed_tutorials_b200.ops import _lib, conv  # noqa: E402
+from tools.conv_check import R50_MULT, _graph_time  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--sizes", default="", help="comma list of H to keep (e.g. 7,14); default all")
+    ap.add_argument("--ops", default="fprop,dgrad,wgrad")
+    ap.add_argument("--widths", default="0,128,64")
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    dev = torch.device("cuda:0")
+    keep = {int(v) for v in a.sizes.split(",") if v}
+    widths = [int(v) for v in a.widths.split(",")]
+    lines = ["| Cin->Cout k/s @H | op | " + " | ".join("bn=%s ms" % (w or "auto") for w in widths) + " | best |",
+             "|---|---|" + "---|" * (len(widths) + 1)]
+    gain = 0.0
+    for (ci, co, k, s, p, H), mult in R50_MULT.items():
+        if keep and H not in keep:
+            continue
+        N = a.batch
+        x = torch.randn(N, ci, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        w = (torch.randn(co, ci, k, k, device=dev) / (ci * k * k) ** 0.5).to(torch.bfloat16).contiguous(
+            memory_format=torch.channels_last)
+        Ho = (H + 2 * p - k) // s + 1
+        dy = torch.randn(N, co, Ho, Ho, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        fns = {"fprop": lambda: conv.conv_fprop(x, w, s, p),
+               "dgrad": lambda: conv.conv_dgrad(dy, w, x.shape, s, p),
+               "wgrad": lambda: conv.conv_wgrad(x, dy, w.shape, s, p)}
+        for op in a.ops.split(","):
+            ts = []
+            for bn in widths:
+                _lib.lib().b2_conv_set_tile_n(bn)
+                try:
+                    ts.append(_graph_time(fns[op]))
+                except Exception:  # noqa: BLE001
+                    ts.append(float("nan"))
+                    torch.cuda.synchronize()
+            _lib.lib().b2_conv_set_tile_n(0)
+            best = min(range(len(ts)), key=lambda i: ts[i] if ts[i] == ts[i] else 1e9)
+            gain += mult * (ts[0] - ts[best])
+            lines.append("| %d->%d %d/%d @%d | %s | " % (ci, co, k, s, H, op) + " | ".join("%.4f" % t for t in ts) +
+                         " | bn=%s |" % (widths[best] or "auto"))
+            print(lines[-1], flush=True)
+    text = ("# N-tile width sweep, batch %d (ms per call, graph of 20 launches, best of 5)\n\n" % a.batch +
+            "Picking the best width per row instead of the default would save %.3f ms per ResNet-50 step.\n\n" % gain +
+            "\n".join(lines) + "\n")
+    if a.out:
+        with open(a.out, "w") as fh:
+            fh.write(text)
+    print(text)
+
+
+if __name__ == "__main__":
+    main()
