@@ -1101,36 +1101,47 @@ __global__ void __launch_bounds__(KIND == WGRAD ? kThreads2W : kThreads2 + 32 * 
           }
         }
       } else if (KIND != WGRAD) {
-        long long orow_idx = m;
-        if (KIND == DGRAD && p.cls > 1 && ok) {
+        // Class-strided dgrad: GEMM row m is pixel (n, i, j) of the parity class grid and lands on pixel
+        // (cls*i + ph, cls*j + pw) of dx, so the tile is not a TMA box. Each warp transposes 32 rows x 64 columns
+        // (128 bytes per row, 16-byte pieces XOR-swizzled by the row) through its own 4 KB of the panel buffers and
+        // stores 4 rows x 128 contiguous bytes per instruction; straight from the registers an instruction touches 32
+        // rows with 16 bytes each, which runs at half the store rate (tools/red_probe.cu) and bounds these kernels.
+        int pix = -1;
+        if (ok) {
           int n, i, j;
           decode_pix(m, p.rowH, p.rowW, n, i, j);
-          orow_idx = ((long long)n * p.outH + (i * p.cls + p.ph)) * p.outW + (j * p.cls + p.pw);
+          pix = (n * p.outH + (i * p.cls + p.ph)) * p.outW + (j * p.cls + p.pw);
         }
-        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_ld + it.n0;
+        uint8_t* stage = epi_smem + ((eg << 2) | quad) * 4096;
+        const int rsub = lane >> 3, piece = lane & 7;
+        __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + it.n0 + piece * 8;
 #pragma unroll 1
-        for (int c = eg; c < BN / 32; c += 2) {
-          uint32_t v[32];
-          tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          if (ok) {
+        for (int cc = eg * 2; cc < BN / 32; cc += 4) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld32(taddr + (cc + h) * 32, v);
+            tmem_ld_wait();
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const int col = it.n0 + c * 32 + q * 8;
-              if (col + 8 > p.Ncols) break;
-              if (p.bias) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                  v[8 * q + e] = __float_as_uint(__uint_as_float(v[8 * q + e]) + __ldg(p.bias + col + e));
-              }
               uint4 o;
               o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
               o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
               o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
               o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
-              st_v4(orow + c * 32 + q * 8, o);
+              *reinterpret_cast<uint4*>(stage + lane * 128 + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
             }
           }
+          __syncwarp();
+          const bool col_ok = it.n0 + cc * 32 + piece * 8 + 8 <= p.Ncols;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int r = 4 * j + rsub;
+            const uint4 o = *reinterpret_cast<const uint4*>(stage + r * 128 + ((piece ^ (r & 7)) << 4));
+            const int pj = __shfl_sync(0xffffffffu, pix, r);
+            if (pj >= 0 && col_ok) st_v4(obase + (size_t)pj * p.out_ld + cc * 32, o);
+          }
+          __syncwarp();
         }
       } else {
         // fp32 tile -> dW (or a split-K slab). Straight from the registers every warp instruction would touch 32
