@@ -653,6 +653,7 @@ static int bn_fwd_train_impl(const void* y, const void* res, void* z, void* relu
   bn_finalize_kernel<<<C / kFinCh, kFinThreads, 0, st>>>(
       partial, nblk, C, (float)M, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, mean,
       invstd, scale_shift, scale_shift + C, ctx, xg_slot);
+  if (!z) return cudaGetLastError();   // coefficients only: the consumer applies them itself (b2_bn_relu_maxpool_fwd)
   const long long nvec = M * (C / 8);
   const int grid = stream_grid(nvec);
   const __nv_bfloat16* yy = (const __nv_bfloat16*)y;
@@ -703,6 +704,7 @@ extern "C" int b2_bn_fwd_eval(const void* y, const void* res, void* z, long long
   cudaStream_t st = (cudaStream_t)stream;
   bn_eval_coeffs_kernel<<<(C + 127) / 128, 128, 0, st>>>(C, gamma, beta, running_mean, running_var, eps, scale_shift,
                                                        scale_shift + C);
+  if (!z) return cudaGetLastError();   // coefficients only
   const long long nvec = M * (C / 8);
   const int grid = stream_grid(nvec);
   const __nv_bfloat16* yy = (const __nv_bfloat16*)y;

@@ -25,7 +25,15 @@ B2_DEVICE uint4 pack8(const float (&v)[8]) {
 // ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
 // Forward also records which of the 9 taps won (first maximum in (kh,kw) scan order, the tie rule of
 // aten::max_pool2d_with_indices) as one byte per output element, so backward is a pure gather.
+// AFF: x is the raw convolution output and every tap first goes through the BatchNorm affine + ReLU
+// (relu(fma(x, scale, shift)), rounded to bf16 exactly as the stand-alone apply kernel would have stored it), so the
+// normalised full-resolution tensor and its ReLU mask never exist. A window whose maximum is 0 (no tap passed the
+// ReLU) records tap code 9, which matches no position in backward: the gradient that maxpool_bwd scatters then already
+// is the gradient of the BatchNorm output.
+template <bool AFF>
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift,
                                                           __nv_bfloat16* __restrict__ y,
                                                           unsigned char* __restrict__ idx, int N, int H, int W,
                                                           int C8, int Ho, int Wo) {
@@ -41,6 +49,11 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
     unsigned arg[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
+    float sc[8], sh[8];
+    if (AFF) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { sc[j] = __ldg(scale + cv * 8 + j); sh[j] = __ldg(shift + cv * 8 + j); }
+    }
     // all nine taps are requested before the first comparison (clamped addresses, validity applied afterwards): nine
     // independent 16-byte loads in flight per thread instead of a load behind every branch
     uint4 raw[9];
@@ -62,9 +75,19 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
       if (!ok[t]) continue;
       float v[8];
       unpack8(raw[t], v);
+      if (AFF) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          v[j] = __bfloat162float(__float2bfloat16_rn(fmaxf(fmaf(v[j], sc[j], sh[j]), 0.f)));
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j)
         if (v[j] > m[j] || arg[j] == 255u) { m[j] = v[j]; arg[j] = t; }
+    }
+    if (AFF) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (!(m[j] > 0.f)) arg[j] = 9u;
     }
     *reinterpret_cast<uint4*>(y + i * 8) = pack8(m);
     if (idx) {
@@ -387,8 +410,16 @@ typedef __nv_bfloat16 bf16;
 extern "C" int b2_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream) {
   if (C % 8) return cudaErrorInvalidValue;
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  maxpool_fwd_kernel<<<sgrid((long long)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, (bf16*)y, (unsigned char*)idx, N, H, W, C / 8, Ho, Wo);
+  maxpool_fwd_kernel<false><<<sgrid((long long)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, nullptr, nullptr, (bf16*)y, (unsigned char*)idx, N, H, W, C / 8, Ho, Wo);
+  return cudaGetLastError();
+}
+extern "C" int b2_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, void* idx, int N,
+                                      int H, int W, int C, void* stream) {
+  if (C % 8 || !scale || !shift) return cudaErrorInvalidValue;
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  maxpool_fwd_kernel<true><<<sgrid((long long)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, scale, shift, (bf16*)y, (unsigned char*)idx, N, H, W, C / 8, Ho, Wo);
   return cudaGetLastError();
 }
 extern "C" int b2_maxpool_bwd(const void* idx, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W,

@@ -177,6 +177,13 @@ int b2_bn_bwd_partial(const void* dz, const void* z, const void* relu_mask, cons
  * ---------------------------------------------------------------------------------------------- */
 /* 3x3 / stride 2 / pad 1. idx (optional, u8 [N,Ho,Wo,C]) records the winning tap for the backward pass. */
 int b2_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
+/* BatchNorm affine + ReLU + maxpool in one pass over the raw convolution output x: y = maxpool(relu(x*scale+shift))
+ * with the intermediate rounded to bf16 exactly as the separate apply kernel stores it (same values, same winners).
+ * Windows whose maximum is 0 record tap code 9, so b2_maxpool_bwd scatters nothing for them and its result is the
+ * gradient of the BatchNorm output (ReLU backward included). scale / shift: fp32 [C], e.g. the scale_shift vector that
+ * b2_bn_fwd_train* / b2_bn_fwd_eval leave behind when called with z == NULL (coefficients only, no apply pass). */
+int b2_bn_relu_maxpool_fwd(const void* x, const float* scale, const float* shift, void* y, void* idx, int N, int H,
+                           int W, int C, void* stream);
 int b2_maxpool_bwd(const void* idx, const void* dy_a, const void* dy_b, void* dx, int N, int H, int W, int C,
                    void* stream);
 int b2_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);

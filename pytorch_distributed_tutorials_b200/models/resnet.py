@@ -279,6 +279,8 @@ class ResNetEngine:
         self.fuse_bn_bwd = os.environ.get("B200DDP_FUSE_BN_BWD", "1") != "0"
         # strided 1x1 downsample: half-resolution input gradient, read compactly by the BatchNorm backward it feeds
         self.compact_ds_grad = os.environ.get("B200DDP_COMPACT_DS_GRAD", "1") != "0"
+        # bn1 + ReLU applied inside the maxpool kernel (the normalised 112x112 tensor and its mask never exist)
+        self.fuse_stem_pool = os.environ.get("B200DDP_FUSE_STEM_POOL", "1") != "0"
         self._bn_blocks = 0
         self.params = list(model.parameters())
         self.xg = None             # peer-memory context for SyncBatchNorm (handed over by the DDP wrapper)
@@ -351,7 +353,8 @@ class ResNetEngine:
         """ReLU bit mask (1 bit / element): what backward needs instead of re-reading the bf16 output."""
         return torch.empty(y.numel() // 8, dtype=torch.uint8, device=y.device)
 
-    def _bn_apply(self, y, bn, relu, res, training, mask=None, partial_blocks=0):
+    def _bn_apply(self, y, bn, relu, res, training, mask=None, partial_blocks=0, apply=True):
+        """``apply=False``: statistics / running statistics / scale+shift only (returns None)."""
         st = self._bn(bn)
         use_batch_stats = training or bn.running_mean is None
         if use_batch_stats:
@@ -361,9 +364,9 @@ class ResNetEngine:
                                        bn.running_var if track else None,
                                        bn.num_batches_tracked if track else None, mom, bn.eps, relu, st.mean,
                                        st.invstd, st.scale_shift, self._sync_bn_ctx(bn), self._next_xg_slot(bn), mask,
-                                       partial_blocks)
+                                       partial_blocks, apply=apply)
         return native.bn_fwd_eval(y, res, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, relu,
-                                  st.scale_shift)
+                                  st.scale_shift, apply=apply)
 
     def _stem(self, x, training, tape):
         m = self.model
@@ -392,17 +395,22 @@ class ResNetEngine:
             else:
                 y2d = convops.gemm_nt(a, self.stem_wp)
             y = y2d.view(n, ho, wo, 64).permute(0, 3, 1, 2)
+        if self.fuse_stem_pool:
+            # coefficients only; the pooling kernel normalises on load and folds the ReLU backward into its index
+            self._bn_apply(y, m.bn1, True, None, training, None, blocks, apply=False)
+            if tape is not None:
+                tape.append(_Rec(None, y, None, m.conv1, m.bn1, True, stem_a=a))
+            return native.bn_relu_maxpool_fwd(y, self._bn(m.bn1).scale_shift, with_index=tape is not None)
         mask = self._new_mask(y) if tape is not None else None
         z = self._bn_apply(y, m.bn1, True, None, training, mask, blocks)
         if tape is not None:
             tape.append(_Rec(None, y, mask, m.conv1, m.bn1, True, stem_a=a))
-        return z
+        return native.maxpool_fwd(z, with_index=tape is not None)
 
     def _run_forward(self, x, training, tape):
         m = self.model
         self._sync_shadows()
-        z = self._stem(x, training, tape)
-        p, pool_idx = native.maxpool_fwd(z, with_index=tape is not None)
+        p, pool_idx = self._stem(x, training, tape)
         block_tapes = []
         cur = p
         for layer in (m.layer1, m.layer2, m.layer3, m.layer4):
@@ -427,7 +435,7 @@ class ResNetEngine:
             pooled = native.avgpool_fwd(cur)
             logits = convops.gemm_nt(pooled, w_fc, m.fc.bias.detach()).float()
         if tape is not None:
-            tape.append(("head", z.shape, pool_idx, block_tapes, cur.shape, pooled))
+            tape.append(("head", tape[0].y.shape, pool_idx, block_tapes, cur.shape, pooled))
         return logits
 
     # ------------------------------------------------------------------ backward units
@@ -595,7 +603,8 @@ class ResNetEngine:
                 d, _ = self._unit_bwd(recs_main[0], d, None, True, False, grads, given_blocks=blocks_first)
             da, db = (d, None) if pre_blocks > 0 else (d, skip)
         dz = native.maxpool_bwd(pool_idx, stem_shape, da, db)
-        self._unit_bwd(tape[0], dz, None, False, False, grads)
+        # fused stem pooling: dead windows scatter nothing, dz already is the gradient of bn1's output
+        self._unit_bwd(tape[0], dz, None, False, False, grads, pre_masked=self.fuse_stem_pool)
         return grads
 
     # ------------------------------------------------------------------ entry

@@ -46,11 +46,12 @@ def _mc(t):
 
 # ------------------------------------------------------------------------------------------------ batch norm
 def bn_fwd_train(y, res, gamma, beta, running_mean, running_var, nbt, momentum, eps, relu, mean, invstd,
-                 scale_shift, xg=None, xg_slot=0, mask=None, partial_blocks=0):
+                 scale_shift, xg=None, xg_slot=0, mask=None, partial_blocks=0, apply=True):
     """aten::native_batch_norm (training) + relu_ + add_ fused. Returns z. ``mask`` (uint8 [M*C/8], optional)
-    receives one bit per element where the ReLU passed."""
+    receives one bit per element where the ReLU passed. ``apply=False``: statistics, running statistics and the
+    scale/shift vector only (returns None) - the consumer applies them itself (``bn_relu_maxpool_fwd``)."""
     M, C = _mc(y)
-    z = torch.empty_like(y)
+    z = torch.empty_like(y) if apply else None
     if partial_blocks > 0:   # statistics partials already produced by the convolution's epilogue
         e = _lib.lib().b2_bn_fwd_train_partial(ptr(y), ptr(res), ptr(z), ptr(mask), c_ll(M), C, ptr(gamma), ptr(beta),
                                                ptr(running_mean), ptr(running_var), ptr(nbt), c_f(momentum),
@@ -58,24 +59,24 @@ def bn_fwd_train(y, res, gamma, beta, running_mean, running_var, nbt, momentum, 
                                                ptr(bn_partial(y.device)), int(partial_blocks), _xg(xg), xg_slot,
                                                stream_ptr())
         check(e, "b2_bn_fwd_train_partial")
-        count_launch(2)
+        count_launch(2 if apply else 1)
         return z
     e = _lib.lib().b2_bn_fwd_train(ptr(y), ptr(res), ptr(z), ptr(mask), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
                                    ptr(running_var), ptr(nbt), c_f(momentum), c_f(eps), int(relu), ptr(mean),
                                    ptr(invstd), ptr(scale_shift), ptr(bn_partial(y.device)), _xg(xg), xg_slot,
                                    stream_ptr())
     check(e, "b2_bn_fwd_train")
-    count_launch(3)
+    count_launch(3 if apply else 2)
     return z
 
 
-def bn_fwd_eval(y, res, gamma, beta, running_mean, running_var, eps, relu, scale_shift):
+def bn_fwd_eval(y, res, gamma, beta, running_mean, running_var, eps, relu, scale_shift, apply=True):
     M, C = _mc(y)
-    z = torch.empty_like(y)
+    z = torch.empty_like(y) if apply else None
     e = _lib.lib().b2_bn_fwd_eval(ptr(y), ptr(res), ptr(z), c_ll(M), C, ptr(gamma), ptr(beta), ptr(running_mean),
                                   ptr(running_var), c_f(eps), int(relu), ptr(scale_shift), stream_ptr())
     check(e, "b2_bn_fwd_eval")
-    count_launch(2)
+    count_launch(2 if apply else 1)
     return z
 
 
@@ -133,6 +134,20 @@ def maxpool_fwd(x, with_index=True):
     y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
     idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device) if with_index else None
     check(_lib.lib().b2_maxpool_fwd(ptr(x), ptr(y), ptr(idx), n, h, w, c, stream_ptr()), "b2_maxpool_fwd")
+    count_launch()
+    return y, idx
+
+
+def bn_relu_maxpool_fwd(x, scale_shift, with_index=True):
+    """maxpool(relu(x * scale + shift)) in one pass over the raw convolution output (the normalised full-resolution
+    tensor and its ReLU mask never exist). ``scale_shift``: fp32 [2C] as left by ``bn_fwd_train(apply=False)``.
+    ``maxpool_bwd`` of the returned index yields the gradient of the BatchNorm OUTPUT (ReLU backward included)."""
+    n, c, h, w = x.shape
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device) if with_index else None
+    check(_lib.lib().b2_bn_relu_maxpool_fwd(ptr(x), ptr(scale_shift), ptr(scale_shift[c:]), ptr(y), ptr(idx), n, h, w,
+                                            c, stream_ptr()), "b2_bn_relu_maxpool_fwd")
     count_launch()
     return y, idx
 

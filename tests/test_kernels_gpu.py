@@ -171,6 +171,36 @@ def test_maxpool(H):
     assert _rel(dx, xf.grad) < 1e-2
 
 
+@pytest.mark.parametrize("H", [56, 31])
+def test_bn_relu_maxpool_fused_equals_apply_then_pool(H):
+    """BatchNorm affine + ReLU applied inside the pooling kernel: same pooled values and winners as the apply kernel
+    followed by maxpool, bit for bit; windows whose maximum is 0 carry tap code 9, and maxpool_bwd of that index is the
+    gradient of the BatchNorm output (ReLU backward included)."""
+    from pytorch_distributed_tutorials_b200.ops import native
+    torch.manual_seed(5)
+    C = 64
+    y = _bf(torch.randn(3, C, H, H, device=DEV))
+    gamma, beta = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV) * 0.3
+    rm, rv = torch.randn(C, device=DEV) * 0.2, torch.rand(C, device=DEV) + 0.5
+    ss = torch.empty(2 * C, device=DEV)
+    z = native.bn_fwd_eval(y, None, gamma, beta, rm, rv, 1e-5, True, ss)
+    p_ref, idx_ref = native.maxpool_fwd(z)
+    ss2 = torch.empty(2 * C, device=DEV)
+    assert native.bn_fwd_eval(y, None, gamma, beta, rm, rv, 1e-5, True, ss2, apply=False) is None
+    assert torch.equal(ss, ss2)
+    p, idx = native.bn_relu_maxpool_fwd(y, ss2)
+    assert torch.equal(p, p_ref)
+    dead = (p_ref.permute(0, 2, 3, 1) == 0)
+    assert torch.equal(idx[~dead], idx_ref[~dead]) and bool((idx[dead] == 9).all()) and dead.any()
+    da, db = _bf(torch.randn_like(p.float())), _bf(torch.randn_like(p.float()))
+    dz = native.maxpool_bwd(idx, y.shape, da, db)
+    dz_ref = native.maxpool_bwd(idx_ref, y.shape, da, db).float() * (z > 0)
+    assert torch.equal(dz.float(), dz_ref)
+    # fp32 torch for the values (winners of near-ties legitimately differ between bf16 and fp32, so not the gradient)
+    pr = F.max_pool2d(F.relu(F.batch_norm(y.float(), rm, rv, gamma, beta, False, 0.0, 1e-5)), 3, 2, 1)
+    assert _rel(p, pr) < 1e-2
+
+
 def test_avgpool():
     from pytorch_distributed_tutorials_b200.ops import native
     x = _bf(torch.randn(5, 2048, 7, 7, device=DEV))
