@@ -1552,6 +1552,16 @@ static int g_fuse_stats = 1;  // fprop epilogue also produces the BatchNorm stat
 static int g_impl = 2;  // 1 = one tile per CTA (v1), 2 = persistent (v2), 3 = persistent CTA pairs where they fit
 // CTA pairs need a 256-row M tile and at least a 128-wide N tile.
 static bool use_pairs(int bn, long long m_extent) { return g_impl == 3 && (bn == 128 || bn == 256) && m_extent >= 256; }
+// Default build: the CTA-pair kernel (cta_group::2, each CTA stages half of the B tile) takes the plain 1x1 GEMMs
+// with 256-wide tiles and K >= 256 - the evaluation-mode forward and the dgrads that produce no BatchNorm sums.
+// Measured 4-10 % faster than the persistent kernel on every such ResNet-50 shape (profiles/impl_sweep_bs256_r2.md);
+// it has no statistics warps and its wgrad is slower, so everything else stays on v2.
+static int g_pairs_auto = 1;
+extern "C" void b2_conv_set_pairs_auto(int on) { g_pairs_auto = on; }
+static bool auto_pairs(int bn, long long m_extent, int KH, int KW, int kdepth, bool plain) {
+  return g_pairs_auto && g_impl == 2 && g_act_mode != ACT_GATHER && !g_force_bn && plain && KH == 1 && KW == 1 &&
+         bn == 256 && kdepth >= 256 && m_extent >= 256;
+}
 }  // namespace b2
 
 using namespace b2;
@@ -1603,7 +1613,8 @@ static int conv_fprop_impl(const void* x, const void* w, const float* bias, void
   } else if ((e = make_tmap_2d_bf16(&tmA, x, (uint64_t)Cin, (uint64_t)N * H * W, 64, 128))) {
     return e;
   }
-  const bool pairs = use_pairs(bn, M) && mode != ACT_GATHER && Cout % bn == 0;
+  const bool pairs = (use_pairs(bn, M) || auto_pairs(bn, M, KH, KW, K, !stats && !bias)) && mode != ACT_GATHER &&
+                     Cout % bn == 0;
   if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)K, (uint64_t)Cout, 64, pairs ? bn / 2 : bn))) return e;
   ConvParams p{};
   p.src = (const __nv_bfloat16*)x; p.srcH = H; p.srcW = W; p.srcC = Cin;
@@ -1772,7 +1783,10 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
   } else if ((e = make_tmap_2d_bf16(&tmA, dy, (uint64_t)Cout, (uint64_t)N * Ho * Wo, 64, 128))) {
     return e;
   }
-  const bool panelsB = g_panels && g_impl == 2 && mode != ACT_GATHER;   // the persistent (non-pair) kernel runs
+  const bool pairs_d = (use_pairs(bn, M) || auto_pairs(bn, M, KH, KW, Cout, !bnreq && !add && !mask && stride == 1 &&
+                                                                            Cin % bn == 0)) &&
+                       mode != ACT_GATHER;
+  const bool panelsB = g_panels && g_impl == 2 && mode != ACT_GATHER && !pairs_d;   // the persistent kernel runs
   if (panelsB) {
     if ((e = make_tmap_panels_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, bn / 64))) return e;
   } else if ((e = make_tmap_2d_bf16(&tmB, w, (uint64_t)KH * KW * Cin, (uint64_t)Cout, 64, 64))) {
@@ -1790,7 +1804,7 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, int N, int H
   p.kh0 = 0; p.kw0 = 0; p.kstep = 1; p.nth = KH; p.ntw = KW; p.cls = 1; p.outH = H; p.outW = W; p.taps = KH * KW;
   if (mode == ACT_IM2COL) p.stride = 1;
   p.n_tiles = Cin / bn; p.m_tiles = (M + BM - 1) / BM;
-  if (use_pairs(bn, M) && mode != ACT_GATHER) {
+  if (pairs_d) {
     p.m_tiles = (M + 2 * BM - 1) / (2 * BM);
     return launch3_mode<DGRAD>(mode, bn, tmA, tmB, p, p.n_tiles * p.m_tiles, st);
   }

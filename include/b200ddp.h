@@ -59,6 +59,10 @@ void b2_conv_set_wgrad_waves(int n);
  * no slab round trip through the workspace and no second kernel; the order of those additions is not fixed, so two
  * runs can differ in the last bits. 0: slabs + a fixed-order reduce kernel everywhere (run-to-run identical). */
 void b2_conv_set_wgrad_red(int on);
+/* 1 (default): plain 1x1 GEMMs with 256-wide tiles and K >= 256 (no BatchNorm statistics, no bias: the evaluation
+ * forward and the dgrads that feed no BatchNorm sums) run on the CTA-pair kernel (tcgen05 cta_group::2, each CTA of a
+ * 2-cluster stages half of the B tile); 0: persistent single-CTA kernel everywhere. */
+void b2_conv_set_pairs_auto(int on);
 int b2_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                   int stride, int pad, void* stream);
 /* dgrad that also produces the partial sums of the BatchNorm backward whose output gradient it computes (statistics

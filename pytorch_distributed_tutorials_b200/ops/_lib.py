@@ -60,7 +60,8 @@ def lib():
         for env, setter in (("B200DDP_BN_APPLY_BATCHED", "b2_bn_set_apply_batched"),
                             ("B200DDP_BN_REDUCE_VARIANT", "b2_bn_set_reduce_variant"),
                             ("B200DDP_CONV_HALO", "b2_conv_set_halo"),
-                            ("B200DDP_WGRAD_RED", "b2_conv_set_wgrad_red")):
+                            ("B200DDP_WGRAD_RED", "b2_conv_set_wgrad_red"),
+                            ("B200DDP_CONV_PAIRS_AUTO", "b2_conv_set_pairs_auto")):
             v = os.environ.get(env)
             if v is not None and hasattr(_lib, setter):
                 getattr(_lib, setter)(int(v))

@@ -19,12 +19,18 @@ def main():
     ap.add_argument("--sizes", default="", help="comma list of H to keep (e.g. 7,14); default all")
     ap.add_argument("--ops", default="fprop,dgrad,wgrad")
     ap.add_argument("--widths", default="0,128,64")
+    ap.add_argument("--impls", default="", help="comma list of kernel generations (b2_conv_set_impl) to compare "
+                    "instead of tile widths, e.g. 2,3 (3 = CTA pairs, cta_group::2)")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     keep = {int(v) for v in a.sizes.split(",") if v}
     widths = [int(v) for v in a.widths.split(",")]
-    lines = ["| Cin->Cout k/s @H | op | " + " | ".join("bn=%s ms" % (w or "auto") for w in widths) + " | best |",
+    impls = [int(v) for v in a.impls.split(",") if v]
+    if impls:
+        widths = impls
+    label = "impl" if impls else "bn"
+    lines = ["| Cin->Cout k/s @H | op | " + " | ".join("%s=%s ms" % (label, w or "auto") for w in widths) + " | best |",
              "|---|---|" + "---|" * (len(widths) + 1)]
     gain = 0.0
     for (ci, co, k, s, p, H), mult in R50_MULT.items():
@@ -42,20 +48,25 @@ def main():
         for op in a.ops.split(","):
             ts = []
             for bn in widths:
-                _lib.lib().b2_conv_set_tile_n(bn)
+                if impls:
+                    _lib.lib().b2_conv_set_impl(bn)
+                else:
+                    _lib.lib().b2_conv_set_tile_n(bn)
                 try:
                     ts.append(_graph_time(fns[op]))
                 except Exception:  # noqa: BLE001
                     ts.append(float("nan"))
                     torch.cuda.synchronize()
             _lib.lib().b2_conv_set_tile_n(0)
+            _lib.lib().b2_conv_set_impl(2)
             best = min(range(len(ts)), key=lambda i: ts[i] if ts[i] == ts[i] else 1e9)
             gain += mult * (ts[0] - ts[best])
             lines.append("| %d->%d %d/%d @%d | %s | " % (ci, co, k, s, H, op) + " | ".join("%.4f" % t for t in ts) +
-                         " | bn=%s |" % (widths[best] or "auto"))
+                         " | %s=%s |" % (label, widths[best] or "auto"))
             print(lines[-1], flush=True)
-    text = ("# N-tile width sweep, batch %d (ms per call, graph of 20 launches, best of 5)\n\n" % a.batch +
-            "Picking the best width per row instead of the default would save %.3f ms per ResNet-50 step.\n\n" % gain +
+    text = ("# %s sweep, batch %d (ms per call, graph of 20 launches, best of 5)\n\n" %
+            ("Kernel generation" if impls else "N-tile width", a.batch) +
+            "Picking the best column per row instead of the first would save %.3f ms per ResNet-50 step.\n\n" % gain +
             "\n".join(lines) + "\n")
     if a.out:
         with open(a.out, "w") as fh:
