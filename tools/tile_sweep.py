@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--widths", default="0,128,64")
     ap.add_argument("--impls", default="", help="comma list of kernel generations (b2_conv_set_impl) to compare "
                     "instead of tile widths, e.g. 2,3 (3 = CTA pairs, cta_group::2)")
+    ap.add_argument("--wgrad-variants", action="store_true",
+                    help="wgrad only: 256x256 tile single wave (default) vs 128-row tiles with 1 or 2 items per SM")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -30,6 +32,8 @@ def main():
     if impls:
         widths = impls
     label = "impl" if impls else "bn"
+    if a.wgrad_variants:
+        a.ops, widths, label = "wgrad", [0, 1, 2], "variant"   # 0: mt2 on; 1: mt2 off, 1 wave; 2: mt2 off, 2 waves
     lines = ["| Cin->Cout k/s @H | op | " + " | ".join("%s=%s ms" % (label, w or "auto") for w in widths) + " | best |",
              "|---|---|" + "---|" * (len(widths) + 1)]
     gain = 0.0
@@ -48,7 +52,10 @@ def main():
         for op in a.ops.split(","):
             ts = []
             for bn in widths:
-                if impls:
+                if a.wgrad_variants:
+                    _lib.lib().b2_conv_set_wgrad_mt2(0 if bn else 1)
+                    _lib.lib().b2_conv_set_wgrad_waves(2 if bn == 2 else 1)
+                elif impls:
                     _lib.lib().b2_conv_set_impl(bn)
                 else:
                     _lib.lib().b2_conv_set_tile_n(bn)
@@ -59,6 +66,8 @@ def main():
                     torch.cuda.synchronize()
             _lib.lib().b2_conv_set_tile_n(0)
             _lib.lib().b2_conv_set_impl(2)
+            _lib.lib().b2_conv_set_wgrad_mt2(1)
+            _lib.lib().b2_conv_set_wgrad_waves(1)
             best = min(range(len(ts)), key=lambda i: ts[i] if ts[i] == ts[i] else 1e9)
             gain += mult * (ts[0] - ts[best])
             lines.append("| %d->%d %d/%d @%d | %s | " % (ci, co, k, s, H, op) + " | ".join("%.4f" % t for t in ts) +
