@@ -216,3 +216,21 @@ def test_device_prefetcher_ring_preserves_order_and_values_on_cpu():
         assert len(out) == 8
         for i, (x, y) in enumerate(out):
             assert x.shape[0] == (4 if i < 7 else 2) and bool((x == float(i)).all()) and bool((y == i).all())
+
+
+def test_wgrad_flags_follow_the_determinism_switch():
+    """b2_conv_wgrad's flag word: bit 0 = accumulate, bit 1 = "sum the split-K partials in a fixed order". The second
+    bit follows torch.use_deterministic_algorithms (and B200DDP_WGRAD_RED=0); the launch count the engine reports
+    drops from 2 (GEMM + reduce kernel) to 1 when the sums form in L2."""
+    import torch
+    from pytorch_distributed_tutorials_b200.ops import conv
+    was = torch.are_deterministic_algorithms_enabled()
+    try:
+        torch.use_deterministic_algorithms(False)
+        if conv._WGRAD_RED:
+            assert conv._wgrad_flags(False) == (0, 1) and conv._wgrad_flags(True) == (1, 1)
+        torch.use_deterministic_algorithms(True, warn_only=True)
+        assert conv._wgrad_flags(False) == (2, 2) and conv._wgrad_flags(True) == (3, 2)
+    finally:
+        torch.use_deterministic_algorithms(was)
+
