@@ -23,6 +23,24 @@ B2_DEVICE uint4 pack8(const float (&v)[8]) {
 }
 
 // ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
+// Both pooling kernels are instruction-bound, not memory-bound (ncu: 74 % SM throughput at 27 % of DRAM with one fp32
+// compare / select chain per element and tap), so the running maximum, the winning tap and the scattered gradient all
+// stay PACKED: two bf16 channels per register, one packed compare mask (0xffff per half) per pair and tap.
+B2_DEVICE uint32_t bf2_gt_mask(uint32_t a, uint32_t b) {
+  return __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+}
+B2_DEVICE uint32_t bf2_add(uint32_t a, uint32_t b) {
+  const __nv_bfloat162 r = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&a),
+                                   *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+// relu(round-to-nearest bf16) of two floats in one instruction: lo -> bits 0..15, hi -> bits 16..31
+B2_DEVICE uint32_t pack_bf16x2_relu(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 // Forward also records which of the 9 taps won (first maximum in (kh,kw) scan order, the tie rule of
 // aten::max_pool2d_with_indices) as one byte per output element, so backward is a pure gather.
 // AFF: x is the raw convolution output and every tap first goes through the BatchNorm affine + ReLU
@@ -45,10 +63,9 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
     const int ow = (int)(pix % Wo); pix /= Wo;
     const int oh = (int)(pix % Ho);
     const int n = (int)(pix / Ho);
-    float m[8];
-    unsigned arg[8];
+    uint32_t m[4], arg[4];   // per channel pair: running maxima (bf16x2), winning taps (2 x 16 bit)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 255u; }
+    for (int p = 0; p < 4; ++p) { m[p] = 0xFF80FF80u; arg[p] = 0x00FF00FFu; }   // -inf, "no tap yet"
     float sc[8], sh[8];
     if (AFF) {
 #pragma unroll
@@ -73,27 +90,31 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
       if (!ok[t]) continue;
-      float v[8];
-      unpack8(raw[t], v);
-      if (AFF) {
+      const uint32_t w4[4] = {raw[t].x, raw[t].y, raw[t].z, raw[t].w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          v[j] = __bfloat162float(__float2bfloat16_rn(fmaxf(fmaf(v[j], sc[j], sh[j]), 0.f)));
+      for (int p = 0; p < 4; ++p) {
+        uint32_t z = w4[p];
+        if (AFF)
+          z = pack_bf16x2_relu(fmaf(__uint_as_float(z << 16), sc[2 * p], sh[2 * p]),
+                               fmaf(__uint_as_float(z & 0xffff0000u), sc[2 * p + 1], sh[2 * p + 1]));
+        // strictly greater: the first maximum keeps its tap; -inf start: the first valid tap always enters
+        const uint32_t gt = bf2_gt_mask(z, m[p]);
+        m[p] = (z & gt) | (m[p] & ~gt);
+        arg[p] = ((uint32_t)t * 0x00010001u & gt) | (arg[p] & ~gt);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (v[j] > m[j] || arg[j] == 255u) { m[j] = v[j]; arg[j] = t; }
     }
     if (AFF) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (!(m[j] > 0.f)) arg[j] = 9u;
+      for (int p = 0; p < 4; ++p) {   // maximum 0 after the ReLU: dead window, tap code 9
+        const uint32_t dead = ~bf2_gt_mask(m[p], 0u);
+        arg[p] = (0x00090009u & dead) | (arg[p] & ~dead);
+      }
     }
-    *reinterpret_cast<uint4*>(y + i * 8) = pack8(m);
+    *reinterpret_cast<uint4*>(y + i * 8) = make_uint4(m[0], m[1], m[2], m[3]);
     if (idx) {
-      uint2 o;
-      o.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
-      o.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+      uint2 o;   // byte j = tap of channel j: the low bytes of the four 16-bit fields of two pair registers
+      o.x = __byte_perm(arg[0], arg[1], 0x6420);
+      o.y = __byte_perm(arg[2], arg[3], 0x6420);
       *reinterpret_cast<uint2*>(idx + i * 8) = o;
     }
   }
@@ -102,7 +123,8 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
 // dx[h,w] = sum over the (<=4) windows containing (h,w) of (dy_a [+ dy_b])[window] * [winner(window) == (h,w)].
 // One thread per 2x2 input quad (rows 2a, 2a+1; columns 2b, 2b+1) and 8 channels: exactly the windows
 // {a, a+1} x {b, b+1} touch the quad, so each window's (index, gradient) vectors are loaded once per quad instead
-// of once per pixel.
+// of once per pixel. A position usually wins one window (at most four): the few additions are done in packed bf16,
+// the precision the result is stored in.
 template <bool TWO>
 __global__ void __launch_bounds__(256)
     maxpool_bwd_kernel(const unsigned char* __restrict__ idx, const __nv_bfloat16* __restrict__ dya,
@@ -117,13 +139,13 @@ __global__ void __launch_bounds__(256)
     const int b = (int)(q % Wq); q /= Wq;
     const int a = (int)(q % Hq);
     const int n = (int)(q / Hq);
-    float acc[2][2][8];
+    uint32_t acc[2][2][4];   // [quad row][quad column][channel pair], bf16x2
 #pragma unroll
     for (int r = 0; r < 2; ++r)
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[r][c][j] = 0.f;
+        for (int p = 0; p < 4; ++p) acc[r][c][p] = 0u;
 #pragma unroll
     for (int dh = 0; dh < 2; ++dh) {
       const int oh = a + dh;
@@ -134,13 +156,12 @@ __global__ void __launch_bounds__(256)
         if (ow >= Wo) continue;
         const long long o = (((long long)(n * Ho + oh) * Wo + ow) * C8 + cv) * 8;
         const uint2 id = *reinterpret_cast<const uint2*>(idx + o);
-        float g[8];
-        unpack8(*reinterpret_cast<const uint4*>(dya + o), g);
+        const uint4 ga = *reinterpret_cast<const uint4*>(dya + o);
+        uint32_t g[4] = {ga.x, ga.y, ga.z, ga.w};
         if (TWO) {
-          float g2[8];
-          unpack8(*reinterpret_cast<const uint4*>(dyb + o), g2);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] += g2[j];
+          const uint4 gb = *reinterpret_cast<const uint4*>(dyb + o);
+          g[0] = bf2_add(g[0], gb.x); g[1] = bf2_add(g[1], gb.y);
+          g[2] = bf2_add(g[2], gb.z); g[3] = bf2_add(g[3], gb.w);
         }
         // window (oh, ow) covers rows 2oh-1..2oh+1: quad row r (h = 2a + r) is tap kh = h - (2oh - 1) = r + 1 - 2dh
 #pragma unroll
@@ -151,12 +172,13 @@ __global__ void __launch_bounds__(256)
           for (int c = 0; c < 2; ++c) {
             const int kw = c + 1 - 2 * dw;
             if (kw < 0 || kw > 2) continue;
-            const unsigned code = (unsigned)(kh * 3 + kw);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              acc[r][c][j] += (((id.x >> (8 * j)) & 0xFFu) == code) ? g[j] : 0.f;
-              acc[r][c][4 + j] += (((id.y >> (8 * j)) & 0xFFu) == code) ? g[4 + j] : 0.f;
-            }
+            const uint32_t code4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
+            const uint32_t e0 = __vcmpeq4(id.x, code4), e1 = __vcmpeq4(id.y, code4);   // 0xff per matching channel
+            // byte masks of channels (2p, 2p+1) widened to the two 16-bit halves of pair p
+            acc[r][c][0] = bf2_add(acc[r][c][0], g[0] & __byte_perm(e0, 0u, 0x1100));
+            acc[r][c][1] = bf2_add(acc[r][c][1], g[1] & __byte_perm(e0, 0u, 0x3322));
+            acc[r][c][2] = bf2_add(acc[r][c][2], g[2] & __byte_perm(e1, 0u, 0x1100));
+            acc[r][c][3] = bf2_add(acc[r][c][3], g[3] & __byte_perm(e1, 0u, 0x3322));
           }
         }
       }
@@ -169,7 +191,8 @@ __global__ void __launch_bounds__(256)
       for (int c = 0; c < 2; ++c) {
         const int w = 2 * b + c;
         if (w >= W) continue;
-        *reinterpret_cast<uint4*>(dx + (((long long)(n * H + h) * W + w) * C8 + cv) * 8) = pack8(acc[r][c]);
+        *reinterpret_cast<uint4*>(dx + (((long long)(n * H + h) * W + w) * C8 + cv) * 8) =
+            make_uint4(acc[r][c][0], acc[r][c][1], acc[r][c][2], acc[r][c][3]);
       }
     }
   }

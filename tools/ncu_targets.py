@@ -12,9 +12,30 @@ import torch  # noqa: E402
 from pytorch_distributed_tutorials_b200.ops import conv, native  # noqa: E402
 
 
+def late_round2(dev):
+    """Kernels changed at the end of round 2: class-strided dgrad (transposed epilogue), the CTA-pair kernel on a plain
+    1x1 GEMM, bn1 + ReLU inside the stem's maxpool.
+        ncu ... -k regex:"igemm2_kernel<1, 2|igemm3_kernel|maxpool_fwd" -c 9 python tools/ncu_targets.py late"""
+    N, cl = 256, torch.channels_last
+    dy = torch.randn(N, 128, 28, 28, device=dev).to(torch.bfloat16).contiguous(memory_format=cl)
+    w = (torch.randn(128, 128, 3, 3, device=dev) / 34).to(torch.bfloat16).contiguous(memory_format=cl)
+    x = torch.randn(N, 1024, 14, 14, device=dev).to(torch.bfloat16).contiguous(memory_format=cl)
+    w1 = (torch.randn(512, 1024, 1, 1, device=dev) / 32).to(torch.bfloat16).contiguous(memory_format=cl)
+    y = torch.randn(N, 64, 112, 112, device=dev).to(torch.bfloat16).contiguous(memory_format=cl)
+    ss = torch.cat([torch.ones(64, device=dev), torch.zeros(64, device=dev)])
+    for _ in range(2):
+        conv.conv_dgrad(dy, w, (N, 128, 56, 56), 2, 1)      # 4 parity-class launches
+        conv.conv_fprop(x, w1, 1, 0)                         # plain 1x1, K = 1024 -> CTA pairs
+        native.bn_relu_maxpool_fwd(y, ss)
+    torch.cuda.synchronize()
+    print("ok")
+
+
 def main():
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "late":
+        return late_round2(dev)
     N = 256
     cl = torch.channels_last
     # weight-stationary 3x3, 64 -> 64 @ 56x56: fprop with BN statistics, dgrad with BN-backward sums
