@@ -26,7 +26,8 @@ def late_round2(dev):
     for _ in range(2):
         conv.conv_dgrad(dy, w, (N, 128, 56, 56), 2, 1)      # 4 parity-class launches
         conv.conv_fprop(x, w1, 1, 0)                         # plain 1x1, K = 1024 -> CTA pairs
-        native.bn_relu_maxpool_fwd(y, ss)
+        pooled, pidx = native.bn_relu_maxpool_fwd(y, ss)
+        native.maxpool_bwd(pidx, y.shape, pooled, pooled)
     torch.cuda.synchronize()
     print("ok")
 
