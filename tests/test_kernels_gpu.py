@@ -57,15 +57,18 @@ def test_conv_fprop_dgrad_wgrad(ci, co, k, s, p, H, N):
     assert _rel(dw2, 2 * ref_dw) < 2e-3
 
 
-def test_gemm_helpers_classifier_shapes():
+@pytest.mark.parametrize("rows", [37, 256])
+def test_gemm_helpers_classifier_shapes(rows):
+    """rows = 256 is the benchmark's batch: the classifier's input-gradient GEMM (K = 1000, not a multiple of 64: the
+    last k-block is zero-filled by TMA) then runs on the CTA-pair kernel like every plain 1x1 GEMM with M >= 256."""
     from pytorch_distributed_tutorials_b200.ops import conv
     torch.manual_seed(1)
-    a = torch.randn(37, 2048, device=DEV).to(torch.bfloat16)
+    a = torch.randn(rows, 2048, device=DEV).to(torch.bfloat16)
     w = (torch.randn(1000, 2048, device=DEV) / 45).to(torch.bfloat16)
     b = torch.randn(1000, device=DEV)
     y = conv.gemm_nt(a, w, b)
     assert _rel(y, a.float() @ w.float().t() + b) < 1e-2
-    dy = torch.randn(37, 1000, device=DEV).to(torch.bfloat16)
+    dy = torch.randn(rows, 1000, device=DEV).to(torch.bfloat16)
     assert _rel(conv.gemm_nn(dy, w), dy.float() @ w.float()) < 1e-2
     out = torch.zeros(1000, 2048, device=DEV)
     conv.gemm_tn(dy, a, out)
