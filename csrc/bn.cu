@@ -543,9 +543,10 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// 0 = plain loop, 1 = batched loads x2 @ 4 CTAs/SM, 2 = x4 @ 2 CTAs/SM, 3 = x3 @ 3 CTAs/SM (b2_bn_set_reduce_variant)
-// Default 2: measured on B200 (tools/bn_bench.py, batch 256, reduce + apply of a residual block output):
-// C=256 @56x56 0.546 ms (variant 0) / 0.535 (1) / 0.475 (2) / 0.497 (3); every ResNet-50 shape ranks the same way.
+// 0 = plain loop, 2 = batched loads: 4 row groups in flight, 2 CTAs/SM (b2_bn_set_reduce_variant). Default 2: measured
+// on B200 (tools/bn_bench.py, batch 256, reduce + apply of a residual block output), C=256 @56x56: 0.546 ms plain loop,
+// 0.475 ms batched; the two other batchings that were tried (2 groups @ 4 CTAs/SM: 0.535, 3 groups @ 3 CTAs/SM: 0.497)
+// lost on every ResNet-50 shape and are no longer built.
 static int g_bn_reduce_variant = 2;
 static int g_bn_apply_batched = 1;   // b2_bn_set_apply_batched(0): grid-stride apply kernels again
 
@@ -627,7 +628,7 @@ using namespace b2;
 B2_DEFINE_SPIN_TIMEOUT_SETTER(b2_set_spin_timeout_ns_bn)
 
 extern "C" void b2_bn_set_apply_batched(int on) { g_bn_apply_batched = on; }
-extern "C" void b2_bn_set_reduce_variant(int v) { g_bn_reduce_variant = (v >= 0 && v <= 3) ? v : 0; }
+extern "C" void b2_bn_set_reduce_variant(int v) { g_bn_reduce_variant = (v == 0) ? 0 : 2; }
 extern "C" long long b2_bn_partial_floats(int C) { return (long long)kMaxPartialBlocks * 2 * C; }
 
 static bool bn_shape_ok(int C) { return C % 8 == 0 && C >= 8 && C <= 2048 && (kBnThreads % (C / 8) == 0); }
@@ -819,12 +820,9 @@ static int bn_bwd_impl(const void* dz_a, const void* dz_b, const void* z, const 
   } else if (variant == 0) {
     B2_BWD_DISPATCH(RED, 0);
   } else {
-    const int bps = variant == 1 ? 4 : (variant == 2 ? 2 : 3);
-    long long cap = (long long)host_num_sms() * bps;
+    long long cap = (long long)host_num_sms() * 2;   // two CTAs per SM
     if (nblk > cap) nblk = (int)cap;
-    if (variant == 1) REDV(2, 4);
-    else if (variant == 2) REDV(4, 2);
-    else REDV(3, 3);
+    REDV(4, 2);
   }
 #undef REDV
 #undef REDB

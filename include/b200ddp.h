@@ -116,8 +116,8 @@ void b2_conv_set_impl(int impl);
  * y: conv output [M,C]; z: block output; partial: scratch of b2_bn_partial_floats(C) floats.
  * ---------------------------------------------------------------------------------------------- */
 long long b2_bn_partial_floats(int C);
-/* Tuning: load batching of the backward reduce pass. 0 = plain unrolled loop, 1 = 2 row groups of loads issued back
- * to back @ 4 CTAs/SM, 2 = 4 groups @ 2 CTAs/SM, 3 = 3 groups @ 3 CTAs/SM. */
+/* Tuning: load batching of the backward reduce pass. 0 = plain unrolled loop, anything else (default) = 4 row groups
+ * of loads issued back to back, 2 CTAs/SM. */
 void b2_bn_set_reduce_variant(int v);
 /* 1 (default): backward apply pass with per-thread channel ownership and batched loads; 0: grid-stride kernels. */
 void b2_bn_set_apply_batched(int on);
