@@ -220,6 +220,43 @@ def test_training_loop_with_wrapper_and_fused_sgd_single_gpu():
     assert keys[0] == "module.conv1.weight" and len(keys) == 122
 
 
+def test_gradient_accumulation_under_no_sync_adds_into_the_bucket_slots():
+    """Two backward passes without zero_grad (the first under no_sync): every native gradient writer - wgrad (split-K
+    sums added in L2 on top of what is there, no memset), the stem's wgrad, BatchNorm dgamma / dbeta, the classifier's
+    bias column sum - must ADD into its bucket slot. Against the sum of the two separately computed gradients."""
+    from pytorch_distributed_tutorials_b200.models.resnet import resnet18
+    from pytorch_distributed_tutorials_b200.ops.loss import CrossEntropyLoss
+    from pytorch_distributed_tutorials_b200.parallel import DistributedDataParallel
+    torch.manual_seed(7)
+    ddp = DistributedDataParallel(resnet18().to(DEV), device_ids=[0])
+    crit = CrossEntropyLoss()
+    xs = [torch.randn(16, 3, 64, 64, device=DEV) for _ in range(2)]
+    ys = [torch.randint(0, 1000, (16,), device=DEV) for _ in range(2)]
+    params = [p for p in ddp.parameters() if p.requires_grad]
+
+    def grads_of(batches, accumulate):
+        out = []
+        for p in params:
+            p.grad = None
+        for i, (x, y) in enumerate(batches):
+            if accumulate and i + 1 < len(batches):
+                with ddp.no_sync():
+                    crit(ddp(x), y).backward()
+            else:
+                crit(ddp(x), y).backward()
+            if not accumulate:
+                out.append([p.grad.detach().clone() for p in params])
+                for p in params:
+                    p.grad = None
+        return out if not accumulate else [p.grad.detach().clone() for p in params]
+
+    g1, g2 = grads_of(list(zip(xs, ys)), accumulate=False)
+    acc = grads_of(list(zip(xs, ys)), accumulate=True)
+    for a, b1, b2, p in zip(acc, g1, g2, params):
+        want = b1 + b2
+        assert (a - want).abs().max().item() <= 2e-3 * want.abs().max().item() + 1e-6, tuple(p.shape)
+
+
 def test_native_library_is_loaded():
     from pytorch_distributed_tutorials_b200.ops import _lib
     assert _lib.available()
